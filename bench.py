@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- homotopy signals/sec on B200 (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config C2]
+
+A step = one pass of the hot path over one batch: every rank solves `batch` signals (C2: 65,536 k=32
+signals against a 512x2048 float32 dictionary).  Weak scaling: per-GPU work is fixed as N grows; the
+dictionary is broadcast once over NCCL, signals are rank-local, reports are gathered each step.
+
+  value     signals/s, inputs resident in HBM (device-pointer entry of the C ABI), CUDA-event timed
+  e2e       the same through the host-pointer entry: pinned host Y in, host X + reports out, every step
+  roofline  the contraction kernel Q = A^T P: algorithmic flops 2*M*N per signal-row / its measured time
+  cpu_baseline  the unmodified reference (oracle/_ref) on this box's host cores, bounded sample
+
+--impl reference times the reference's own CPU implementation (oracle/_ref, else the oracle port).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "sparse-solvers_b200"))
+
+import numpy as np  # noqa: E402
+
+CONFIGS = {
+    # BASELINE.json configs[]; C2 is the configuration the metric is quoted on
+    "C1": dict(m=256, n=1024, k=16, dtype="float32", batch=1024, tol=1e-3, max_iter=48),
+    "C2": dict(m=512, n=2048, k=32, dtype="float32", batch=65536, tol=1e-3, max_iter=80),
+    "C5": dict(m=4096, n=16384, k=128, dtype="float32", batch=8192, tol=1e-3, max_iter=272),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
+    ap.add_argument("--batch", type=int, default=None, help="signals per GPU per step (default: the config's)")
+    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--cpu-sample", type=int, default=None, help="signals in the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gather-x", action="store_true", help="also gather the dense coefficients to rank 0 each step")
+    return ap.parse_args()
+
+
+def make_workload(cfg, batch, seed):
+    from sparsesolvers import synth
+    dt = np.dtype(cfg["dtype"])
+    A = synth.dictionary(cfg["m"], cfg["n"], dtype=dt, seed=1234 + 2)
+    Y, X0 = synth.sparse_signals(A, batch, cfg["k"], seed=seed)
+    return A, Y
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_solve(A, Y, cfg, threads):
+    """The reference's CPU path on `threads` host threads (one BLAS thread each: its best throughput mode,
+    BASELINE.md §3).  Returns (seconds, kind, iters)."""
+    from oracle import ref, port
+    if ref.available() and os.path.exists("/root/repo/oracle/_ref/libcblas_fwd.so"):
+        ref.set_blas_threads(1)
+        t0 = time.perf_counter()
+        X, it, err = ref.homotopy(A, Y, cfg["tol"], cfg["max_iter"], threads=threads)
+        return time.perf_counter() - t0, "reference", it
+    os.environ.setdefault("OMP_NUM_THREADS", str(threads))
+    t0 = time.perf_counter()
+    X, it, err = port.homotopy(A, Y, cfg["tol"], cfg["max_iter"])
+    return time.perf_counter() - t0, "port", it
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return None
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        if not sm:
+            return None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def run_reference(args, cfg):
+    """--impl reference: the reference's CPU solver on this box's host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = host_threads()
+    sample = args.cpu_sample or (256 if args.config == "C2" else 64)
+    A, Y = make_workload(cfg, sample, seed=4321)
+    for _ in range(args.warmup):
+        cpu_reference_solve(A, Y[: max(8, sample // 8)], cfg, threads)
+    secs, kind = [], "port"
+    for _ in range(args.steps):
+        s, kind, it = cpu_reference_solve(A, Y, cfg, threads)
+        secs.append(s)
+    total = float(sum(secs))
+    value = sample * args.steps / total
+    line = {
+        "impl": "reference", "metric": "homotopy signals/sec", "value": value, "unit": "signals/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: homotopy A {cfg['m']}x{cfg['n']} float32, k={cfg['k']}, tol {cfg['tol']}, "
+                               f"max_iter {cfg['max_iter']}", "batch_per_step": sample},
+        "cpu_baseline": {"value": value, "unit": "signals/s", "cores": threads, "kind": kind,
+                         "sample": f"{sample} signals of the {args.config} workload per step, {threads} host threads x 1 BLAS thread"},
+        "e2e": {"value": value, "unit": "signals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_b200(args, cfg):
+    import torch
+    import torch.distributed as dist
+    import sparsesolvers as ss
+    from sparsesolvers import distributed as ssd
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    batch = args.batch or cfg["batch"]
+    dt = np.dtype(cfg["dtype"])
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    M, N = cfg["m"], cfg["n"]
+
+    # rank-local signals (weak scaling); the dictionary comes from rank 0 over NCCL
+    A, Y = make_workload(cfg, batch, seed=4321 + 1000 * rank)
+    if world > 1:
+        dA = ssd.broadcast_dictionary(torch.from_numpy(A) if rank == 0 else torch.empty((M, N), dtype=tdt), dist, device=dev)
+    else:
+        dA = torch.from_numpy(A).to(dev)
+    torch.cuda.synchronize()
+
+    import ctypes as C
+    from sparsesolvers._lib import lib, check
+    solver = ss.Homotopy.__new__(ss.Homotopy)            # dictionary already on the device: create_dev
+    solver._sfx, solver._ct = ("f32", C.c_float) if dt == np.float32 else ("f64", C.c_double)
+    solver.dtype, solver.shape, solver.device, solver._h = dt, (M, N), local, C.c_void_p()
+    check(getattr(lib(), f"ssb200_homotopy_create_dev_{solver._sfx}")(
+        C.c_void_p(dA.data_ptr()), C.c_size_t(M), C.c_size_t(N), C.c_ssize_t(dA.stride(0)), C.c_ssize_t(dA.stride(1)),
+        C.c_int(local), C.byref(solver._h)))
+    solver.set_contraction_path(args.path)
+
+    dY = torch.from_numpy(Y).to(dev)
+    dX = torch.empty((batch, N), dtype=tdt, device=dev)
+    dIt = torch.empty(batch, dtype=torch.int32, device=dev)
+    dErr = torch.empty(batch, dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_dev():
+        solver.solve_batch_ptr(dY.data_ptr(), batch, M, dX.data_ptr(), N, dIt.data_ptr(), dErr.data_ptr(),
+                               cfg["tol"], cfg["max_iter"], True, stream)
+        if world > 1:
+            ssd.gather_reports(dIt, dErr, dist)
+            if args.gather_x:
+                ssd.gather_coefficients(dX, dist)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_dev()
+    solver.reset_counters()
+    solver.set_timing(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_dev()
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = e0.elapsed_time(e1)
+    solver.set_timing(False)
+    counters, timing = solver.counters(), solver.timing()
+    iters_mean = float(dIt.to(torch.float64).mean().item())
+    converged = float((dErr <= cfg["tol"]).to(torch.float64).mean().item())
+
+    # ---- end to end: pinned host buffers through the host-pointer entry, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hY = torch.from_numpy(Y).pin_memory()
+        hX = torch.empty((batch, N), dtype=tdt).pin_memory()
+        hIt = torch.empty(batch, dtype=torch.int32).pin_memory()
+        hErr = torch.empty(batch, dtype=torch.float64).pin_memory()
+
+        def step_host():
+            solver.solve_batch_ptr(hY.data_ptr(), batch, M, hX.data_ptr(), N, hIt.data_ptr(), hErr.data_ptr(),
+                                   cfg["tol"], cfg["max_iter"], False)
+        step_host()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_host()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        assert torch.equal(hIt, dIt.cpu()), "host-pointer and device-pointer entries disagree"
+    if world > 1:
+        t = torch.tensor([ms, e2e_s if not args.no_e2e else 0.0], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_max = float(t[0].item()), float(t[1].item())
+    else:
+        e2e_max = e2e_s if not args.no_e2e else 0.0
+    if not args.no_e2e:
+        isz = dt.itemsize
+        e2e = {"value": world * batch * args.steps / e2e_max, "unit": "signals/s",
+               "h2d_bytes_per_step": world * batch * M * isz, "d2h_bytes_per_step": world * batch * (N * isz + 4 + 8)}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks, peak_src = measured_peaks()
+    # roofline of the dominant kernel (contraction): algorithmic flops = 2*M*N per signal-row
+    flops = 2.0 * M * N * counters["contraction_rows"]
+    achieved = flops / (timing["contraction_ms"] * 1e-3) / 1e12 if timing["contraction_ms"] > 0 else 0.0
+    tensor_path = args.path != "simt" and dt == np.float32
+    # fp32-equivalent tensor peak of the 3xTF32 scheme: TF32 dense = bf16/2, three MMAs per product
+    peak = peaks["bf16_tflops_sustained"] / 6.0
+    roofline = {"kernel": "contract (Q = A^T P)", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": None,
+                "peak_source": f"{peak_src} bf16_tflops_sustained / 6 (TF32 = bf16/2, 3 MMAs per fp32 product)",
+                "launches": counters["contractions"], "avg_launch_ms": timing["contraction_ms"] / max(1, counters["contractions"]),
+                "share_of_step": timing["contraction_ms"] / ms, "step_kernel_share": timing["step_ms"] / ms,
+                "path": "tcgen05 3xTF32" if tensor_path else "simt fp32"}
+    whole = {"achieved": 2.0 * M * N * world * batch * args.steps * (iters_mean + 1) / (ms * 1e-3) / 1e12,
+             "unit": "TFLOP/s", "note": "whole-solve algorithmic flops 2*M*N*(iters+1) per signal / step time"}
+    whole["frac"] = whole["achieved"] / (peak * world)
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        threads = host_threads()
+        sample = args.cpu_sample or (512 if args.config == "C2" else 64)
+        sample = min(sample, batch)
+        secs, kind, it_ref = cpu_reference_solve(A, Y[:sample], cfg, threads)
+        cpu = {"value": sample / secs, "unit": "signals/s", "cores": threads, "kind": kind,
+               "sample": f"first {sample} signals of rank 0's batch, {threads} host threads x 1 BLAS thread, {secs:.1f} s",
+               "iters_match_gpu": int((it_ref == dIt[:sample].cpu().numpy().astype(np.uint32)).sum())}
+
+    line = {
+        "metric": "homotopy signals/sec", "value": world * batch * args.steps / (ms * 1e-3), "unit": "signals/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if dt == np.float32 else "f64",
+        "data": "synthetic",
+        "config": {"workload": f"{args.config}: homotopy A {M}x{N} {cfg['dtype']}, {batch} k={cfg['k']} signals per GPU, "
+                               f"tol {cfg['tol']}, max_iter {cfg['max_iter']}",
+                   "batch_per_gpu": batch, "mean_iters": iters_mean, "converged_frac": converged,
+                   "l2": "working set (C,Q,X: 3 x %.0f MB per GPU) exceeds the 126 MB L2; no explicit flush" % (batch * N * dt.itemsize / 1e6),
+                   "contraction_path": args.path, "gather_x": bool(args.gather_x)},
+        "e2e": e2e, "gpu_launches": counters["launches"], "roofline": roofline, "whole_solve": whole,
+        "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    cfg = CONFIGS[args.config]
+    if args.impl == "reference":
+        run_reference(args, cfg)
+    else:
+        run_b200(args, cfg)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,163 @@
+/* ssb200.h -- C ABI of the B200-native l1 hot path (ss::homotopy / ss::irls solve loops).
+ *
+ * This is the drop-in boundary.  In the reference the four `Policy::run` overloads
+ *   homotopy_policy::run(A, y, tol, max_iter, x)   src/lib.cpp:30-46
+ *   irls_policy::run(state, y, tol, max_iter, x)   src/lib.cpp:61-73
+ * dispatch through kernelpp::run<solve_homotopy / solve_irls> (kernel_invoke.h:236-249) to the
+ * CPU solver loops (src/solvers/homotopy-cpu.cpp:185-297, src/solvers/irls-cpu.cpp:62-146), which
+ * do their arithmetic through the OpenBLAS wrapper (src/linalg/blas_wrapper.h:99-400).  The entry
+ * points below replace that dispatch + BLAS layer for this path: a maintainer re-implements the four
+ * overloads as calls into this header (INTEGRATION.md shows the stub) and nothing above
+ * include/ss/*.h changes.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ / torch types cross the boundary.
+ *   - every function returns an ssb200_status; nothing throws, nothing aborts (the reference
+ *     abort()s when BLAS cannot be loaded, src/linalg/blas_wrapper.cpp:39-49; here that is
+ *     SSB200_COMPUTE_MODE_UNAVAILABLE).  ssb200_status_string() gives the kernelpp wording
+ *     (third_party/kernelpp/include/kernelpp/kernel.h:122-133) so `maybe<report>` error strings
+ *     stay what callers saw before.
+ *   - strides are in ELEMENTS, as ss::ndspan carries them (include/ss/ndspan.h:28-31); any
+ *     row-major / column-major / padded / sub-view dictionary is accepted
+ *     (src/linalg/blas_wrapper.h:73-93; bindings/python/tests/test_binding.py:31-68).
+ *   - there is NO CPU fallback: without an sm_100 device the create call fails.
+ *   - a handle may be used from one host thread at a time (the reference's solve is
+ *     re-entrant; here the handle owns its stream and workspace, so callers that want
+ *     concurrency create one handle per thread).
+ */
+#ifndef SSB200_H
+#define SSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum ssb200_status {
+    SSB200_OK = 0,
+    SSB200_KERNEL_FAILED = 1,            /* "Kernel Failed"            kernel.h:122-133 */
+    SSB200_COMPUTE_MODE_DISABLED = 2,    /* "Compute Mode Disabled"   */
+    SSB200_COMPUTE_MODE_UNAVAILABLE = 3, /* "Compute Mode Unavailable": no sm_100 device */
+    SSB200_KERNEL_NOT_DEFINED = 4,       /* "Kernel Not Defined"      */
+    SSB200_CANCELLED = 5,                /* "Cancelled"               */
+    SSB200_INVALID_ARGUMENT = 6          /* shape / pointer checks the reference only assert()s
+                                            (homotopy-cpu.cpp:193-199) */
+} ssb200_status;
+
+const char* ssb200_status_string(int status);
+/* detail of the last failure on the calling thread (CUDA error text, shape message) */
+const char* ssb200_last_error(void);
+/* {major, minor, patch} of the reference API this library stands in for (binding.cpp:42-46) */
+void ssb200_version(int v[3]);
+/* number of visible sm_100 devices (0 when there is none / no driver) */
+int ssb200_device_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Homotopy.  Replaces ss::solver<T, homotopy_policy> state + solve (include/ss/ss.h:98-115).
+ *
+ * create: uploads the M x N dictionary once and repacks it atom-major ("A^T row-major"), builds
+ *   the TF32 hi/lo split used by the tensor-core contraction and the Gram matrix A^T A.  The
+ *   reference state is a NON-owning view of A (include/ss/policies.h:42); here the device copy is
+ *   owned by the handle, so a caller that edits A in place between solves (the reference bench
+ *   does, src/solvers/homotopy_bench.cpp:38-48) calls ssb200_homotopy_refresh_*.
+ * solve: one signal, host pointers (homotopy-cpu.cpp:185-275).  x (length N) is overwritten.
+ *   *solution_error is |c|_inf at exit, *iter the number of loop passes (policies.h:25-32).
+ * solve_batch: `batch` independent signals, row b of Y at Y + b*ldy (host memory), x_b written
+ *   to X + b*ldx (host memory).  New functionality (the reference has no batching, ss.h:50);
+ *   each signal's result equals what solve() returns for it.
+ * solve_batch_dev: same with DEVICE pointers for Y, X, iters, errors (no host copies);
+ *   work is enqueued on `stream` (a cudaStream_t, may be NULL) and the call returns after the
+ *   stream has been synchronised.
+ */
+int ssb200_homotopy_create_f32(const float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                               int device, void** handle);
+int ssb200_homotopy_create_f64(const double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                               int device, void** handle);
+/* device-resident dictionary (dA on `device`, strides in elements) -- used after an NCCL broadcast of A */
+int ssb200_homotopy_create_dev_f32(const float* dA, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                                   int device, void** handle);
+int ssb200_homotopy_create_dev_f64(const double* dA, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                                   int device, void** handle);
+int ssb200_homotopy_refresh_f32(void* handle, const float* A, ptrdiff_t row_stride, ptrdiff_t col_stride);
+int ssb200_homotopy_refresh_f64(void* handle, const double* A, ptrdiff_t row_stride, ptrdiff_t col_stride);
+
+int ssb200_homotopy_solve_f32(void* handle, const float* y, ptrdiff_t y_stride, float tolerance, uint32_t max_iterations,
+                              float* x, ptrdiff_t x_stride, uint32_t* iter, double* solution_error);
+int ssb200_homotopy_solve_f64(void* handle, const double* y, ptrdiff_t y_stride, double tolerance, uint32_t max_iterations,
+                              double* x, ptrdiff_t x_stride, uint32_t* iter, double* solution_error);
+
+int ssb200_homotopy_solve_batch_f32(void* handle, const float* Y, size_t batch, size_t ldy, float tolerance,
+                                    uint32_t max_iterations, float* X, size_t ldx, uint32_t* iters, double* errors);
+int ssb200_homotopy_solve_batch_f64(void* handle, const double* Y, size_t batch, size_t ldy, double tolerance,
+                                    uint32_t max_iterations, double* X, size_t ldx, uint32_t* iters, double* errors);
+
+int ssb200_homotopy_solve_batch_dev_f32(void* handle, const float* dY, size_t batch, size_t ldy, float tolerance,
+                                        uint32_t max_iterations, float* dX, size_t ldx, uint32_t* d_iters,
+                                        double* d_errors, void* stream);
+int ssb200_homotopy_solve_batch_dev_f64(void* handle, const double* dY, size_t batch, size_t ldy, double tolerance,
+                                        uint32_t max_iterations, double* dX, size_t ldx, uint32_t* d_iters,
+                                        double* d_errors, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * IRLS.  Replaces ss::solver<T, irls_policy>: irls_state(A) = Householder QR of A
+ * (src/lib.cpp:51-57, src/linalg/qr_decomposition.h:93-190; requires M >= N, :101) and the
+ * solve loop (src/solvers/irls-cpu.cpp:62-124).  spd_failure is a successful result
+ * (include/ss/policies.h:58-71); solution_error is the final epsilon (irls-cpu.cpp:123).
+ */
+int ssb200_irls_create_f32(const float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                           int device, void** handle);
+int ssb200_irls_create_f64(const double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                           int device, void** handle);
+int ssb200_irls_solve_f32(void* handle, const float* y, ptrdiff_t y_stride, float tolerance, uint32_t max_iterations,
+                          float* x, ptrdiff_t x_stride, uint32_t* iter, double* solution_error, uint8_t* spd_failure);
+int ssb200_irls_solve_f64(void* handle, const double* y, ptrdiff_t y_stride, double tolerance, uint32_t max_iterations,
+                          double* x, ptrdiff_t x_stride, uint32_t* iter, double* solution_error, uint8_t* spd_failure);
+int ssb200_irls_solve_batch_f32(void* handle, const float* Y, size_t batch, size_t ldy, float tolerance,
+                                uint32_t max_iterations, float* X, size_t ldx, uint32_t* iters, double* errors,
+                                uint8_t* spd_failures);
+int ssb200_irls_solve_batch_f64(void* handle, const double* Y, size_t batch, size_t ldy, double tolerance,
+                                uint32_t max_iterations, double* X, size_t ldx, uint32_t* iters, double* errors,
+                                uint8_t* spd_failures);
+int ssb200_irls_solve_batch_dev_f32(void* handle, const float* dY, size_t batch, size_t ldy, float tolerance,
+                                    uint32_t max_iterations, float* dX, size_t ldx, uint32_t* d_iters, double* d_errors,
+                                    uint8_t* d_spd_failures, void* stream);
+int ssb200_irls_solve_batch_dev_f64(void* handle, const double* dY, size_t batch, size_t ldy, double tolerance,
+                                    uint32_t max_iterations, double* dX, size_t ldx, uint32_t* d_iters, double* d_errors,
+                                    uint8_t* d_spd_failures, void* stream);
+
+/* frees a homotopy or IRLS handle (solver destructor, include/ss/ss.h:52-55) */
+void ssb200_destroy(void* handle);
+
+/* ------------------------------------------------------------------------------------------
+ * Utilities next to the path (include/ss/ss.h:79-93, src/lib.cpp:78-112), batched on the device.
+ *   reconstruct: Y[b] = A * X[b]          (ss::reconstruct_signal)
+ *   norm_l1:     A[:, j] /= sum_i |A[i, j]|  in place on the host array (ss::norm_l1)
+ */
+int ssb200_reconstruct_batch_f32(void* homotopy_handle, const float* X, size_t batch, size_t ldx, float* Y, size_t ldy);
+int ssb200_reconstruct_batch_f64(void* homotopy_handle, const double* X, size_t batch, size_t ldx, double* Y, size_t ldy);
+int ssb200_norm_l1_f32(float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
+int ssb200_norm_l1_f64(double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
+
+/* ------------------------------------------------------------------------------------------
+ * Instrumentation (bench.py / tests; not part of the reference API).
+ *   counters[0] = kernel launches since the last reset
+ *   counters[1] = launches of the contraction kernel (Q = A^T P)
+ *   counters[2] = signal-rows pushed through the contraction kernel
+ *   counters[3] = lockstep iterations executed
+ *   timing (when enabled the contraction launches are bracketed by CUDA events on the handle's
+ *   stream):  ms[0] = summed contraction time, ms[1] = summed step-kernel time
+ *   path: 0 = choose by batch size (product behaviour), 1 = force the SIMT contraction,
+ *         2 = force the tcgen05 contraction (float32 only)
+ */
+int ssb200_reset_counters(void* handle);
+int ssb200_get_counters(void* handle, uint64_t counters[4]);
+int ssb200_set_timing(void* handle, int enabled);
+int ssb200_get_timing(void* handle, double ms[2]);
+int ssb200_set_contraction_path(void* handle, int path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSB200_H */

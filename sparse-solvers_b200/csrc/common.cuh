@@ -1,0 +1,117 @@
+// Shared host/device helpers of libssb200 (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cfloat>
+#include <cstddef>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/ssb200.h"
+
+namespace ssb {
+
+// ---- error plumbing: CUDA failures become an ssb200_status + a thread-local message ----------
+void set_last_error(const std::string& msg);
+
+struct cuda_failure { cudaError_t err; const char* what; const char* file; int line; };
+
+#define SSB_CUDA(expr)                                                                  \
+    do {                                                                                \
+        cudaError_t _e = (expr);                                                        \
+        if (_e != cudaSuccess) throw ::ssb::cuda_failure{ _e, #expr, __FILE__, __LINE__ }; \
+    } while (0)
+
+struct invalid_argument { std::string what; };
+#define SSB_REQUIRE(cond, msg)                                   \
+    do { if (!(cond)) throw ::ssb::invalid_argument{ msg }; } while (0)
+
+// ---- small RAII device buffer --------------------------------------------------------------
+struct dev_buffer {
+    void* p = nullptr;
+    size_t bytes = 0;
+    dev_buffer() = default;
+    dev_buffer(const dev_buffer&) = delete;
+    dev_buffer& operator=(const dev_buffer&) = delete;
+    ~dev_buffer() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    // grows only; contents are not preserved
+    void reserve(size_t nbytes) {
+        if (nbytes <= bytes) return;
+        release();
+        SSB_CUDA(cudaMalloc(&p, nbytes));
+        bytes = nbytes;
+    }
+    template <typename U> U* as() const { return static_cast<U*>(p); }
+};
+
+struct pinned_buffer {
+    void* p = nullptr;
+    size_t bytes = 0;
+    ~pinned_buffer() { if (p) cudaFreeHost(p); }
+    void reserve(size_t nbytes) {
+        if (nbytes <= bytes) return;
+        if (p) cudaFreeHost(p);
+        p = nullptr; bytes = 0;
+        SSB_CUDA(cudaMallocHost(&p, nbytes));
+        bytes = nbytes;
+    }
+    template <typename U> U* as() const { return static_cast<U*>(p); }
+};
+
+inline size_t round_up(size_t v, size_t to) { return (v + to - 1) / to * to; }
+
+template <typename T> struct num_traits;
+template <> struct num_traits<float>  { static __host__ __device__ float  max() { return FLT_MAX; } static __host__ __device__ float  eps() { return FLT_EPSILON; } };
+template <> struct num_traits<double> { static __host__ __device__ double max() { return DBL_MAX; } static __host__ __device__ double eps() { return DBL_EPSILON; } };
+
+// ---- device reductions ----------------------------------------------------------------------
+#ifdef __CUDACC__
+
+// (value, index) candidates ordered lexicographically: smaller value first, then lower index --
+// the left-most strict decrease of the reference's scan (homotopy-cpu.cpp:156-160).
+template <typename T>
+__device__ __forceinline__ bool cand_less(T va, uint32_t ia, T vb, uint32_t ib) {
+    return va < vb || (va == vb && ia < ib);
+}
+
+template <typename T>
+__device__ __forceinline__ void warp_argmin(T& v, uint32_t& i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        T ov = __shfl_xor_sync(0xffffffffu, v, o);
+        uint32_t oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (cand_less(ov, oi, v, i)) { v = ov; i = oi; }
+    }
+}
+
+// first index of the largest value (cblas i?amax, homotopy-cpu.cpp:32-37)
+template <typename T>
+__device__ __forceinline__ void warp_argmax_first(T& v, uint32_t& i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        T ov = __shfl_xor_sync(0xffffffffu, v, o);
+        uint32_t oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_max(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace ssb

@@ -1,0 +1,385 @@
+// Per-signal kernels of the batched homotopy solve (sm_100a).
+//
+// One CTA owns one signal for one lockstep iteration.  Everything the reference does between two
+// full-dictionary products is in homotopy_step_kernel:
+//   min-gamma search over the join and leave candidate sets      homotopy-cpu.cpp:122-163
+//   active-set toggle + online update of (A_G^T A_G)^-1           homotopy-cpu.cpp:166-183,
+//                                                                 src/linalg/online_inverse.h:183-293
+//   x += gamma * d (old direction), correlation update, |c|_inf   homotopy-cpu.cpp:252-255,:270
+//   new direction d_G = inv * sign(c_G, tol)                      homotopy-cpu.cpp:259-266
+//   p = A_G d_G for the next contraction  q = A^T p               homotopy-cpu.cpp:112-120
+//
+// What differs from the reference by construction (all algebraically identical):
+//   - c is advanced as c -= gamma*q (q = A^T A d is already there) instead of re-forming
+//     A^T (y - A x) from scratch (homotopy-cpu.cpp:87-98);
+//   - A_G^T v for a joining atom v is read from the precomputed Gram matrix G = A^T A instead of
+//     K dot products (online_inverse.h:217-218);
+//   - the active set is kept in slot (insertion) order with a bitmask for membership, not as a
+//     sorted rank index (src/linalg/rank_index.h): no result depends on the order, only the
+//     summation order inside inv*u does.  A leaving atom's slot is refilled by the last slot.
+#pragma once
+
+#include "common.cuh"
+
+namespace ssb {
+
+template <typename T>
+struct HomArgs {
+    int N;            // atoms
+    int ldc;          // leading dimension of C and Q (= Npad)
+    int Mp;           // padded signal length (= Mpad), also ld of At
+    int ldp;          // leading dimension of the P buffers
+    int Kmax;         // capacity of the per-signal active set
+    const T* At;      // [Npad][Mp]  atom-major dictionary, zero padded
+    const T* G;       // [N][ldg]    Gram matrix A^T A
+    int ldg;
+    T* C;             // [Bc][ldc]   correlations, by signal
+    const T* Q;       // [rows][ldc] contraction result, by position in `act`
+    T* X;             // signal-major coefficients (caller's output)
+    size_t ldx;
+    uint32_t* gam;    // [Bc][Kmax]  active atoms in slot order
+    T* dG;            // [Bc][Kmax]  direction on the active atoms
+    T* Ginv;          // [Bc][Kmax*Kmax], leading dimension Kmax
+    T* lam;           // [Bc]        |c|_inf
+    int* Kcur;        // [Bc]
+    uint32_t* iters;  // [Bc]        report: loop passes
+    double* errs;     // [Bc]        report: solution_error
+    const int* act;   // [rows]      position -> signal (nullptr: identity)
+    int* act_next;    // compacted list for the next iteration
+    int* next_count;
+    T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
+    T* Pn_lo;         //             TF32 lo part (only when split != 0)
+    int split;
+    T tol;
+    uint32_t max_iter;
+    uint32_t it;      // lockstep iteration number, 1-based
+};
+
+__device__ __forceinline__ float tf32_rna(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+// writes V consecutive values of p as full precision or as a TF32 hi/lo pair
+template <typename T, int V>
+__device__ __forceinline__ void store_rhs(T* hi, T* lo, int split, const T (&v)[V]) {
+    if constexpr (sizeof(T) == 4) {
+        if (split) {
+            float h[V], l[V];
+#pragma unroll
+            for (int e = 0; e < V; ++e) { h[e] = tf32_rna(v[e]); l[e] = tf32_rna(v[e] - h[e]); }
+            *reinterpret_cast<int4*>(hi) = *reinterpret_cast<const int4*>(h);
+            *reinterpret_cast<int4*>(lo) = *reinterpret_cast<const int4*>(l);
+            return;
+        }
+    }
+    *reinterpret_cast<int4*>(hi) = *reinterpret_cast<const int4*>(v);
+}
+
+// Y (caller layout) -> first right-hand sides, zero padded to ldp
+template <typename T>
+__global__ void stage_signals_kernel(const T* __restrict__ Y, size_t ldy, int M, int rows,
+                                     T* __restrict__ P, T* __restrict__ Plo, int ldp, int split)
+{
+    constexpr int V = 16 / sizeof(T);
+    const size_t total = (size_t)rows * (ldp / V);
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = e / (ldp / V);
+        const int m0 = (int)(e % (ldp / V)) * V;
+        T v[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) v[k] = (m0 + k < M) ? Y[r * ldy + m0 + k] : T(0);
+        store_rhs<T, V>(P + r * ldp + m0, Plo ? Plo + r * ldp + m0 : nullptr, split, v);
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ T sign_tol(T v, T tol) { return v > tol ? T(1) : (v < -tol ? T(-1) : T(0)); }
+
+// p = sum_k d[k] * At[gam[k]][:]  for the CTA's signal, written to row `row` of the next P
+template <typename T, int THREADS>
+__device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, const uint32_t* s_gam, const T* s_d, int K)
+{
+    constexpr int V = 16 / sizeof(T);
+    T* pn = a.Pn + (size_t)row * a.ldp;
+    T* pl = a.split ? a.Pn_lo + (size_t)row * a.ldp : nullptr;
+    for (int m0 = threadIdx.x * V; m0 < a.Mp; m0 += THREADS * V) {
+        T acc[V];
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[e] = T(0);
+        for (int k = 0; k < K; ++k) {
+            T av[V];
+            *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
+            const T dk = s_d[k];
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc[e] += av[e] * dk;
+        }
+        store_rhs<T, V>(pn + m0, pl ? pl + m0 : nullptr, a.split, acc);
+    }
+}
+
+// Initial state (homotopy-cpu.cpp:201-229): x = 0, c = A^T y (in Q), lambda = |c|_inf with the FIRST
+// maximal index, G = {idx}, inv = 1/|a_idx|^2, d = sign(lambda, tol) * inv -- the sign of |c|, not of c
+// (the reference quirk at :223-224, reproduced).
+template <typename T, int THREADS>
+__global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
+{
+    constexpr int V = 16 / sizeof(T);
+    constexpr int NW = THREADS / 32;
+    __shared__ T red_v[NW];
+    __shared__ uint32_t red_i[NW];
+    __shared__ uint32_t s_gam[1];
+    __shared__ T s_d[1];
+
+    const int s = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const T* q = a.Q + (size_t)s * a.ldc;
+    T* c = a.C + (size_t)s * a.ldc;
+    T* x = a.X + (size_t)s * a.ldx;
+
+    T best = T(-1);
+    uint32_t bidx = 0xffffffffu;
+    for (int i0 = tid * V; i0 < a.ldc; i0 += THREADS * V) {
+        T qv[V];
+        *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
+        *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(qv);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const int i = i0 + e;
+            if (i < a.N) {
+                x[i] = T(0);
+                const T av = fabs(qv[e]);
+                if (av > best) { best = av; bidx = (uint32_t)i; }
+            }
+        }
+    }
+    warp_argmax_first(best, bidx);
+    if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+    __syncthreads();
+    if (warp == 0) {
+        best = lane < NW ? red_v[lane] : T(-1);
+        bidx = lane < NW ? red_i[lane] : 0xffffffffu;
+        warp_argmax_first(best, bidx);
+        if (lane == 0) {
+            if (bidx == 0xffffffffu) { bidx = 0; best = fabs(q[0]); }  // all-NaN correlations
+            const T nrm = sqrt(a.G[(size_t)bidx * a.ldg + bidx]);       // online_inverse.h:193-201
+            const T inv = T(1) / (nrm * nrm);
+            const T d0 = sign_tol(best, a.tol) * inv;
+            a.gam[(size_t)s * a.Kmax] = bidx;
+            a.dG[(size_t)s * a.Kmax] = d0;
+            a.Ginv[(size_t)s * a.Kmax * a.Kmax] = inv;
+            a.lam[s] = best;
+            a.Kcur[s] = 1;
+            s_gam[0] = bidx;
+            s_d[0] = d0;
+        }
+    }
+    __syncthreads();
+    write_rhs<T, THREADS>(a, s, s_gam, s_d, 1);
+}
+
+// One homotopy iteration for one signal (homotopy-cpu.cpp:236-272).
+template <typename T, int THREADS>
+__global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
+{
+    constexpr int V = 16 / sizeof(T);
+    constexpr int NW = THREADS / 32;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ T red_v[NW];
+    __shared__ uint32_t red_i[NW];
+    __shared__ T sh_gamma, sh_lam;
+    __shared__ uint32_t sh_idx;
+    __shared__ int sh_slot, sh_row;
+
+    const int KC = a.Kmax + 1;
+    T* s_d = reinterpret_cast<T*>(smem_raw);
+    T* s_u1 = s_d + KC;
+    T* s_u2 = s_u1 + KC;
+    T* s_cg = s_u2 + KC;
+    uint32_t* s_gam = reinterpret_cast<uint32_t*>(s_cg + KC);
+    uint32_t* mask = s_gam + KC;
+    const int mask_words = (a.ldc + 31) >> 5;
+
+    const int pos = blockIdx.x;
+    const int s = a.act ? a.act[pos] : pos;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    const int K = a.Kcur[s];
+    const T lam = a.lam[s];
+    uint32_t* gam = a.gam + (size_t)s * a.Kmax;
+    T* dG = a.dG + (size_t)s * a.Kmax;
+    T* Ginv = a.Ginv + (size_t)s * a.Kmax * a.Kmax;
+    const int ldi = a.Kmax;
+    T* c = a.C + (size_t)s * a.ldc;
+    const T* q = a.Q + (size_t)pos * a.ldc;
+    T* x = a.X + (size_t)s * a.ldx;
+    const T TMAX = num_traits<T>::max();
+
+    for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
+    for (int k = tid; k < K; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }
+    __syncthreads();
+    for (int k = tid; k < K; k += THREADS) atomicOr(&mask[s_gam[k] >> 5], 1u << (s_gam[k] & 31));
+    __syncthreads();
+
+    // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index
+    T best = TMAX;
+    uint32_t bidx = 0xffffffffu;
+    for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
+        T cv[V], qv[V];
+        *reinterpret_cast<int4*>(cv) = *reinterpret_cast<const int4*>(c + i0);
+        *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
+        const uint32_t mw = mask[i0 >> 5] >> (i0 & 31);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            const int i = i0 + e;
+            if (i < a.N && !((mw >> e) & 1u)) {
+                const T dl = T(1) - qv[e], dr = T(1) + qv[e];
+                if (dl != T(0)) { const T t = (lam - cv[e]) / dl; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                if (dr != T(0)) { const T t = (lam + cv[e]) / dr; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+            }
+        }
+    }
+    for (int k = tid; k < K; k += THREADS) {   // leave candidates, -x_i / d_i (:129-137)
+        const uint32_t i = s_gam[k];
+        const T t = -x[i] / s_d[k];
+        if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
+    }
+    warp_argmin(best, bidx);
+    if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+    __syncthreads();
+    if (warp == 0) {
+        best = lane < NW ? red_v[lane] : TMAX;
+        bidx = lane < NW ? red_i[lane] : 0xffffffffu;
+        warp_argmin(best, bidx);
+        if (lane == 0) {
+            if (bidx == 0xffffffffu) bidx = 0;   // no candidate: (max, 0) -- the caller toggles column 0 (:122-123)
+            sh_gamma = best;
+            sh_idx = bidx;
+            sh_slot = -1;
+        }
+    }
+    __syncthreads();
+    const T gamma = sh_gamma;
+    const uint32_t idx = sh_idx;
+    const bool present = (mask[idx >> 5] >> (idx & 31)) & 1u;
+    if (present)
+        for (int k = tid; k < K; k += THREADS) if (s_gam[k] == idx) sh_slot = k;
+    const int Knew = present ? K - 1 : K + 1;
+
+    if (Knew == 0) {   // :248-249: the last atom left; x, c and lambda stay as they were
+        if (tid == 0) { a.iters[s] = a.it; a.errs[s] = (double)lam; a.Kcur[s] = 0; }
+        return;
+    }
+
+    // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
+    for (int k = tid; k < K; k += THREADS) x[s_gam[k]] += gamma * s_d[k];
+
+    // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
+    T mx = T(0);
+    for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
+        T cv[V], qv[V];
+        *reinterpret_cast<int4*>(cv) = *reinterpret_cast<const int4*>(c + i0);
+        *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            cv[e] = cv[e] - gamma * qv[e];
+            if (i0 + e < a.N) mx = max(mx, fabs(cv[e]));
+        }
+        *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(cv);
+    }
+    mx = warp_max(mx);
+    if (lane == 0) red_v[warp] = mx;
+    __syncthreads();   // also orders sh_slot and the c stores
+    if (tid == 0) {
+        T m = red_v[0];
+        for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
+        sh_lam = m;
+    }
+
+    // ---- toggle idx and update inv = (A_G^T A_G)^-1 (inverse_add_or_remove, :166-183)
+    if (!present) {
+        // online_inverse.h:203-249 (bordering); the new atom takes slot K
+        for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];   // u1 = A_G^T v
+        const T dot = a.G[(size_t)idx * a.ldg + idx];                                         // v.v
+        __syncthreads();
+        for (int r = warp; r < K; r += NW) {                                                  // u2 = inv u1
+            T acc = T(0);
+            for (int k = lane; k < K; k += 32) acc += Ginv[(size_t)r * ldi + k] * s_u1[k];
+            acc = warp_sum(acc);
+            if (lane == 0) s_u2[r] = acc;
+        }
+        __syncthreads();
+        T uu = T(0);
+        for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
+        uu = warp_sum(uu);
+        const T dd = T(1) / (dot - uu);                                                       // :228
+        for (int e = tid; e < K * K; e += THREADS) {                                          // inv += d u2 u2^T
+            const int r = e / K, k = e - r * K;
+            Ginv[(size_t)r * ldi + k] += (dd * s_u2[r]) * s_u2[k];
+        }
+        for (int r = tid; r < K; r += THREADS) {                                              // border -d u2, corner d
+            const T u3 = -dd * s_u2[r];
+            Ginv[(size_t)r * ldi + K] = u3;
+            Ginv[(size_t)K * ldi + r] = u3;
+        }
+        if (tid == 0) { Ginv[(size_t)K * ldi + K] = dd; s_gam[K] = idx; gam[K] = idx; }
+    } else {
+        // online_inverse.h:253-293; the leaving atom sits in slot j
+        const int j = sh_slot;
+        const T dd = Ginv[(size_t)j * ldi + j];
+        const T sc = -(T(1) / dd);
+        for (int r = tid; r < K; r += THREADS) s_u1[r] = Ginv[(size_t)r * ldi + j] * sc;       // u = -col/d
+        __syncthreads();
+        for (int e = tid; e < K * K; e += THREADS) {                                          // inv -= d u u^T
+            const int r = e / K, k = e - r * K;
+            if (r != j && k != j) Ginv[(size_t)r * ldi + k] += (-dd * s_u1[r]) * s_u1[k];
+        }
+        __syncthreads();
+        const int last = K - 1;
+        if (j != last) {   // refill slot j with the last slot (reads touch row/col `last` only, writes never do)
+            for (int k = tid; k < last; k += THREADS) {
+                const int kk = (k == j) ? last : k;
+                const T vrow = Ginv[(size_t)last * ldi + kk];
+                const T vcol = Ginv[(size_t)kk * ldi + last];
+                Ginv[(size_t)j * ldi + k] = vrow;
+                Ginv[(size_t)k * ldi + j] = vcol;
+            }
+            if (tid == 0) { const uint32_t g = s_gam[last]; s_gam[j] = g; gam[j] = g; }
+        }
+    }
+    __syncthreads();
+
+    // ---- d_G = inv * sign(c_G, tol) (:259-263); the tolerance is also the sign dead-band
+    for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(c[s_gam[k]], a.tol);
+    __syncthreads();
+    for (int r = warp; r < Knew; r += NW) {
+        T acc = T(0);
+        for (int k = lane; k < Knew; k += 32) acc += Ginv[(size_t)r * ldi + k] * s_cg[k];
+        acc = warp_sum(acc);
+        if (lane == 0) { s_d[r] = acc; dG[r] = acc; }
+    }
+    const T lam_new = sh_lam;
+    const bool cont = (a.it < a.max_iter) && (lam_new > a.tol);   // :272
+    if (tid == 0) {
+        a.lam[s] = lam_new;
+        a.Kcur[s] = Knew;
+        if (cont) {
+            const int row = atomicAdd(a.next_count, 1);
+            a.act_next[row] = s;
+            sh_row = row;
+        } else {
+            a.iters[s] = a.it;
+            a.errs[s] = (double)lam_new;   // :274
+        }
+    }
+    __syncthreads();
+    if (cont) write_rhs<T, THREADS>(a, sh_row, s_gam, s_d, Knew);
+}
+
+template <typename T>
+inline size_t homotopy_step_smem(int Kmax, int ldc) {
+    return (size_t)(Kmax + 1) * (4 * sizeof(T) + sizeof(uint32_t)) + (size_t)((ldc + 31) / 32) * sizeof(uint32_t);
+}
+
+}  // namespace ssb

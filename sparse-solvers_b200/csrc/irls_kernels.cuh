@@ -1,0 +1,186 @@
+// IRLS solve loop on the device (reference: src/solvers/irls-cpu.cpp:39-124 with
+// src/linalg/cholesky_decomposition.h:57-103).  One CTA owns one signal for its WHOLE solve: unlike
+// homotopy there is no full-dictionary product inside the loop once Q^T y is known, so nothing has
+// to run in lockstep across signals.
+//
+// With A = QR (thin, M >= N) the reference forms, every iteration,
+//     G = Q^T (Q o w),  L = chol(tril(G)),  s = L^-T L^-1 (Q^T y),  x = R^-1 Q^T (Q s).
+// Here Q^T y comes from one batched contraction, and E = Q^T Q (computed once per dictionary, with
+// its rounding-level off-diagonals kept) gives G_ij = E_ij * w_j and Q^T (Q s) = E s: the same
+// numbers up to summation order, N^2 instead of M N^2 work per iteration.  The SPD test
+// (sqrt(pivot) <= eps, cholesky_decomposition.h:80-83) is evaluated on that G, because it is how
+// most solves end.
+#pragma once
+
+#include "common.cuh"
+
+namespace ssb {
+
+template <typename T>
+struct IrlsArgs {
+    int N;              // columns of A
+    int lde;            // leading dimension of E and S (= Npad)
+    const T* E;         // [N][lde]   Q^T Q
+    const T* Rc;        // [N][N]     R stored column-major: Rc[i*N + k] = R[k][i]
+    const T* S;         // [rows][lde] Q^T y
+    T* X; size_t ldx;   // output
+    T* L;               // [rows][N*N] Cholesky factor, column-major: L[k*N + i] = l_ik
+    T* vec;             // [rows][4*N]  w | xnext | s | (spare)
+    uint32_t* iters; double* errs; uint8_t* spd;
+    T tol; uint32_t max_iter;
+};
+
+template <typename T, int THREADS>
+__device__ __forceinline__ T block_sum(T v, T* red) {
+    constexpr int NW = THREADS / 32;
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    T t = T(0);
+#pragma unroll
+    for (int w = 0; w < NW; ++w) t += red[w];
+    return t;
+}
+
+template <typename T, int THREADS>
+__global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
+{
+    constexpr int NW = THREADS / 32;
+    __shared__ T red[NW];
+    __shared__ T red2[NW];
+    __shared__ T sh_piv;
+    __shared__ int sh_bad;
+
+    const int N = a.N;
+    const size_t b = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    T* x = a.X + b * a.ldx;
+    T* L = a.L + b * (size_t)N * N;
+    T* w = a.vec + b * 4 * (size_t)N;
+    T* xn = w + N;
+    T* sv = xn + N;
+    const T* qty = a.S + b * (size_t)a.lde;
+    const T EPS = num_traits<T>::eps();
+    const double ex = ((double)(T)0.9) / 2.0 - 1.0;   // p = 0.9 (irls-cpu.cpp:70)
+
+    for (int j = tid; j < N; j += THREADS) { x[j] = T(0); w[j] = T(1); xn[j] = T(1); }   // :82-85
+    uint32_t iter = 0;
+    int spd_error = 0;
+    T abstol = T(1), eps = T(1), second = T(1);
+    __syncthreads();
+
+    do {
+        // ---- irls_newton (:39-60).  G_ij = E_ij w_j on the lower triangle, left-looking Cholesky.
+        int bad = 0;
+        for (int j = 0; j < N; ++j) {
+            const T wj = w[j];
+            for (int i = j + tid; i < N; i += THREADS) {
+                T acc = T(0);
+                for (int k = 0; k < j; ++k) acc += L[(size_t)k * N + i] * L[(size_t)k * N + j];
+                L[(size_t)j * N + i] = a.E[(size_t)i * a.lde + j] * wj - acc;
+            }
+            __syncthreads();
+            const T ajj = sqrt(L[(size_t)j * N + j]);
+            if (ajj <= EPS) bad = 1;           // NaN pivots pass, as in the reference
+            const T inv = T(1) / ajj;
+            __syncthreads();
+            for (int i = j + tid; i < N; i += THREADS) L[(size_t)j * N + i] *= inv;
+            __syncthreads();
+        }
+        if (bad) { spd_error = 1; break; }      // :94-97, x keeps the previous iterate
+
+        // s = L^-T L^-1 (Q^T y)  (cholesky_decomposition.h:93-103)
+        for (int j = tid; j < N; j += THREADS) sv[j] = qty[j];
+        __syncthreads();
+        for (int i = 0; i < N; ++i) {           // forward, column sweeps
+            const T zi = sv[i] / L[(size_t)i * N + i];
+            __syncthreads();
+            if (tid == 0) sv[i] = zi;
+            for (int k = i + 1 + tid; k < N; k += THREADS) sv[k] -= L[(size_t)i * N + k] * zi;
+            __syncthreads();
+        }
+        for (int i = N - 1; i >= 0; --i) {      // backward, dot with column i of L below the diagonal
+            T acc = T(0);
+            for (int k = i + 1 + tid; k < N; k += THREADS) acc += L[(size_t)i * N + k] * sv[k];
+            acc = block_sum<T, THREADS>(acc, red);
+            if (tid == 0) sv[i] = (sv[i] - acc) / L[(size_t)i * N + i];
+            __syncthreads();
+        }
+        // xnext = Q^T (Q s) = E s  (:55-57)
+        for (int r = warp; r < N; r += NW) {
+            T acc = T(0);
+            for (int k = lane; k < N; k += 32) acc += a.E[(size_t)r * a.lde + k] * sv[k];
+            acc = warp_sum(acc);
+            if (lane == 0) xn[r] = acc;
+        }
+        __syncthreads();
+        // R xnext = xnext, R upper triangular (:58), column sweeps from the last unknown
+        for (int i = N - 1; i >= 0; --i) {
+            const T xi = xn[i] / a.Rc[(size_t)i * N + i];
+            __syncthreads();
+            if (tid == 0) xn[i] = xi;
+            for (int k = tid; k < i; k += THREADS) xn[k] -= a.Rc[(size_t)i * N + k] * xi;
+            __syncthreads();
+        }
+
+        // ---- thresholding and reweighting (:100-114)
+        T mx = -num_traits<T>::max();
+        for (int j = tid; j < N; j += THREADS) mx = max(mx, xn[j]);   // signed max
+        mx = warp_max(mx);
+        if (lane == 0) red[warp] = mx;
+        __syncthreads();
+        mx = red[0];
+        for (int q = 1; q < NW; ++q) mx = max(mx, red[q]);
+        abstol = mx * a.tol;
+        __syncthreads();
+        T top = -num_traits<T>::max(), sec = -num_traits<T>::max();
+        for (int j = tid; j < N; j += THREADS) {
+            T v = xn[j];
+            if (v < abstol) v = T(0);           // also zeroes every negative entry
+            xn[j] = v;
+            x[j] = v;
+            if (v > top) { sec = top; top = v; } else if (v > sec) sec = v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {      // second-largest value (nth_element at :107)
+            const T ot = __shfl_xor_sync(0xffffffffu, top, o), os = __shfl_xor_sync(0xffffffffu, sec, o);
+            const T nt = max(top, ot);
+            sec = max(min(top, ot), max(sec, os));
+            top = nt;
+        }
+        if (lane == 0) { red[warp] = top; red2[warp] = sec; }
+        __syncthreads();
+        top = red[0]; sec = red2[0];
+        for (int q = 1; q < NW; ++q) {
+            const T ot = red[q], os = red2[q];
+            const T nt = max(top, ot);
+            sec = max(min(top, ot), max(sec, os));
+            top = nt;
+        }
+        second = (N > 1) ? sec : top;
+        if (second / (T)N < eps) eps = second / (T)N;                 // :110
+        __syncthreads();
+        T sw = T(0);
+        for (int j = tid; j < N; j += THREADS) {
+            const T base = x[j] * x[j] + eps;
+            const T wv = (T)pow((double)base, ex);                    // :113
+            w[j] = wv;
+            sw += wv;
+        }
+        sw = block_sum<T, THREADS>(sw, red);
+        for (int j = tid; j < N; j += THREADS) w[j] /= sw;            // :114
+        __syncthreads();
+        iter++;
+    } while (iter < a.max_iter && second > abstol);                   // :118
+
+    __syncthreads();
+    T sx = T(0);
+    for (int j = tid; j < N; j += THREADS) sx += x[j];
+    sx = block_sum<T, THREADS>(sx, red);
+    for (int j = tid; j < N; j += THREADS) x[j] /= sx;                // :121
+    if (tid == 0) { a.iters[b] = iter; a.errs[b] = (double)eps; a.spd[b] = (uint8_t)spd_error; }
+    (void)sh_piv; (void)sh_bad;
+}
+
+}  // namespace ssb

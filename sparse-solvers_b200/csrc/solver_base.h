@@ -1,0 +1,81 @@
+// Host-side handle shared by the homotopy and IRLS drivers: device, stream, counters, event timing.
+#pragma once
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace ssb {
+
+enum class SolverKind : int { HomotopyF32 = 1, HomotopyF64 = 2, IrlsF32 = 3, IrlsF64 = 4 };
+
+struct device_guard {
+    int prev = -1;
+    explicit device_guard(int dev) { cudaGetDevice(&prev); if (prev != dev) SSB_CUDA(cudaSetDevice(dev)); else prev = -1; }
+    ~device_guard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct SolverBase {
+    SolverKind kind;
+    int device = 0;
+    cudaStream_t stream = nullptr;       // the handle's own stream (host-pointer entry points)
+    uint64_t counters[4] = { 0, 0, 0, 0 };
+    bool timing = false;
+    double ms[2] = { 0.0, 0.0 };
+    int contraction_path = 0;            // 0 auto, 1 SIMT, 2 tcgen05
+
+    // pairs of events bracketing launches of class `cls` on the current solve's stream
+    struct span { cudaEvent_t a, b; int cls; };
+    std::vector<span> spans;
+    std::vector<cudaEvent_t> event_pool;
+
+    SolverBase(SolverKind k, int dev) : kind(k), device(dev) {
+        SSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    }
+    virtual ~SolverBase() {
+        for (auto e : event_pool) cudaEventDestroy(e);
+        for (auto& s : spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+        if (stream) cudaStreamDestroy(stream);
+    }
+
+    cudaEvent_t get_event() {
+        if (!event_pool.empty()) { cudaEvent_t e = event_pool.back(); event_pool.pop_back(); return e; }
+        cudaEvent_t e;
+        SSB_CUDA(cudaEventCreate(&e));
+        return e;
+    }
+    // usage: auto t = begin_span(cls, st); launch...; end_span(t, st);
+    int begin_span(int cls, cudaStream_t st) {
+        if (!timing) return -1;
+        span s{ get_event(), get_event(), cls };
+        SSB_CUDA(cudaEventRecord(s.a, st));
+        spans.push_back(s);
+        return (int)spans.size() - 1;
+    }
+    void end_span(int id, cudaStream_t st) {
+        if (id < 0) return;
+        SSB_CUDA(cudaEventRecord(spans[id].b, st));
+    }
+    // call after the stream has been synchronised
+    void collect_spans() {
+        for (auto& s : spans) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) ms[s.cls] += t;
+            event_pool.push_back(s.a);
+            event_pool.push_back(s.b);
+        }
+        spans.clear();
+    }
+};
+
+// contract_tc.cu: Q[r][n] = sum_m At[n][m] P[r][m] on the tcgen05 pipe, 3xTF32 (hi*hi + hi*lo + lo*hi).
+// At_hi/At_lo: [n_pad][mp], P_hi/P_lo: [rows_alloc][mp] with rows_alloc % 256 == 0 (rows beyond
+// `rows` are computed but not stored), Q: [rows][ldq].  n_pad % 128 == 0, mp % 32 == 0.
+struct TcPlan;   // holds the TMA descriptors of one (At, P, Q) buffer set
+TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp,
+                       const float* P_hi, const float* P_lo, int rows_alloc);
+void tc_plan_destroy(TcPlan*);
+void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream);
+bool tc_supported(int n_pad, int mp);
+
+}  // namespace ssb

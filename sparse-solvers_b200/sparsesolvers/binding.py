@@ -1,0 +1,214 @@
+"""Host-side mirror of the reference's pybind11 module (bindings/python/sparsesolvers/binding.cpp).
+
+    Homotopy(A).solve(b, tolerance=10*eps, max_iterations=100) -> (x, HomotopyReport)    binding.cpp:79-111
+    Irls(A).solve(b, ...)                                      -> (x, IrlsReport)
+    version() -> [major, minor, patch]                                                   binding.cpp:42-46
+
+A may be any 2-D float32/float64 array view (row subsets, column subsets, transposes: its strides are
+passed through, binding.cpp:21-37); b must have the dictionary's dtype exactly (`noconvert`, :108).
+`solve_batch` is additive: many signals against one dictionary in one call.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import SolverError, check, lib
+
+__all__ = ["Homotopy", "Irls", "HomotopyReport", "IrlsReport", "version", "SolverError",
+           "reconstruct_signal", "norm_l1"]
+
+
+def version():
+    v = (C.c_int * 3)()
+    lib().ssb200_version(v)
+    return list(v)
+
+
+class HomotopyReport:
+    """include/ss/policies.h:25-32"""
+    def __init__(self, iter=0, solution_error=0.0):
+        self.iter = int(iter)
+        self.solution_error = float(solution_error)
+
+    def __repr__(self):
+        return f"HomotopyReport(iter={self.iter}, solution_error={self.solution_error})"
+
+
+class IrlsReport:
+    """include/ss/policies.h:58-71"""
+    def __init__(self, iter=0, solution_error=0.0, spd_failure=False):
+        self.iter = int(iter)
+        self.solution_error = float(solution_error)
+        self.spd_failure = bool(spd_failure)
+
+    def __repr__(self):
+        return (f"IrlsReport(iter={self.iter}, solution_error={self.solution_error}, "
+                f"spd_failure={self.spd_failure})")
+
+
+_SFX = {np.dtype(np.float32): ("f32", C.c_float), np.dtype(np.float64): ("f64", C.c_double)}
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+class _Solver:
+    _name = None
+
+    def __init__(self, A, device=0):
+        A = np.asarray(A)
+        if A.ndim != 2:
+            raise ValueError("A must be 2-dimensional")
+        if A.dtype not in _SFX:
+            raise TypeError("A must be float32 or float64")          # binding.cpp:82-85 overloads
+        self._sfx, self._ct = _SFX[A.dtype]
+        self.dtype = A.dtype
+        self.shape = A.shape
+        self.device = device
+        self._h = C.c_void_p()
+        rs, cs = A.strides[0] // A.itemsize, A.strides[1] // A.itemsize
+        fn = getattr(lib(), f"ssb200_{self._name}_create_{self._sfx}")
+        check(fn(_ptr(A), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]), C.c_ssize_t(rs), C.c_ssize_t(cs),
+                 C.c_int(device), C.byref(self._h)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            lib().ssb200_destroy(h)
+            self._h = C.c_void_p()
+
+    def _check_signal(self, b, ndim):
+        if not isinstance(b, np.ndarray) or b.dtype != self.dtype:
+            raise TypeError(f"signal must be a numpy array of dtype {self.dtype}")   # py::arg().noconvert()
+        if b.ndim != ndim or b.shape[-1] != self.shape[0]:
+            raise ValueError(f"signal must have {self.shape[0]} entries")
+
+    def _defaults(self, tolerance, max_iterations):
+        if tolerance is None:
+            tolerance = 10 * np.finfo(self.dtype).eps                # binding.cpp:94
+        return self._ct(tolerance), C.c_uint32(int(max_iterations))
+
+    # instrumentation used by bench.py and the tests
+    def counters(self):
+        c = (C.c_uint64 * 4)()
+        check(lib().ssb200_get_counters(self._h, c))
+        return dict(launches=c[0], contractions=c[1], contraction_rows=c[2], iterations=c[3])
+
+    def reset_counters(self):
+        check(lib().ssb200_reset_counters(self._h))
+
+    def set_timing(self, on):
+        check(lib().ssb200_set_timing(self._h, C.c_int(1 if on else 0)))
+
+    def timing(self):
+        ms = (C.c_double * 2)()
+        check(lib().ssb200_get_timing(self._h, ms))
+        return dict(contraction_ms=ms[0], step_ms=ms[1])
+
+    def set_contraction_path(self, path):
+        check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2}[path])))
+
+
+class Homotopy(_Solver):
+    _name = "homotopy"
+
+    def solve(self, b, tolerance=None, max_iterations=100):
+        self._check_signal(b, 1)
+        tol, mi = self._defaults(tolerance, max_iterations)
+        x = np.empty(self.shape[1], dtype=self.dtype)
+        it, err = C.c_uint32(), C.c_double()
+        fn = getattr(lib(), f"ssb200_homotopy_solve_{self._sfx}")
+        check(fn(self._h, _ptr(b), C.c_ssize_t(b.strides[0] // b.itemsize), tol, mi, _ptr(x), C.c_ssize_t(1),
+                 C.byref(it), C.byref(err)))
+        return x, HomotopyReport(it.value, err.value)
+
+    def solve_batch(self, Y, tolerance=None, max_iterations=100, out=None):
+        """Y: (B, M) rows are signals.  Returns X (B, N), iters (B,) uint32, solution_errors (B,) float64."""
+        self._check_signal(Y, 2)
+        if Y.strides[1] != Y.itemsize:
+            Y = np.ascontiguousarray(Y)
+        tol, mi = self._defaults(tolerance, max_iterations)
+        B = Y.shape[0]
+        X = out if out is not None else np.empty((B, self.shape[1]), dtype=self.dtype)
+        iters = np.empty(B, dtype=np.uint32)
+        errs = np.empty(B, dtype=np.float64)
+        fn = getattr(lib(), f"ssb200_homotopy_solve_batch_{self._sfx}")
+        check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
+                 _ptr(X), C.c_size_t(X.strides[0] // X.itemsize), _ptr(iters), _ptr(errs)))
+        return X, iters, errs
+
+    def solve_batch_ptr(self, y_ptr, batch, ldy, x_ptr, ldx, iters_ptr, errs_ptr, tolerance, max_iterations,
+                        device_pointers, stream=0):
+        """Raw-pointer entry (pinned host buffers or device buffers owned by the caller, e.g. torch tensors)."""
+        tol, mi = self._defaults(tolerance, max_iterations)
+        if device_pointers:
+            fn = getattr(lib(), f"ssb200_homotopy_solve_batch_dev_{self._sfx}")
+            check(fn(self._h, C.c_void_p(y_ptr), C.c_size_t(batch), C.c_size_t(ldy), tol, mi, C.c_void_p(x_ptr),
+                     C.c_size_t(ldx), C.c_void_p(iters_ptr), C.c_void_p(errs_ptr), C.c_void_p(stream)))
+        else:
+            fn = getattr(lib(), f"ssb200_homotopy_solve_batch_{self._sfx}")
+            check(fn(self._h, C.c_void_p(y_ptr), C.c_size_t(batch), C.c_size_t(ldy), tol, mi, C.c_void_p(x_ptr),
+                     C.c_size_t(ldx), C.c_void_p(iters_ptr), C.c_void_p(errs_ptr)))
+
+    def refresh(self, A):
+        """Re-uploads an edited dictionary of the same shape (the reference state is a non-owning view,
+        include/ss/policies.h:42; its bench edits A in place between solves, homotopy_bench.cpp:38-48)."""
+        A = np.asarray(A)
+        if A.shape != self.shape or A.dtype != self.dtype:
+            raise ValueError("refresh must keep the dictionary's shape and dtype")
+        rs, cs = A.strides[0] // A.itemsize, A.strides[1] // A.itemsize
+        check(getattr(lib(), f"ssb200_homotopy_refresh_{self._sfx}")(self._h, _ptr(A), C.c_ssize_t(rs), C.c_ssize_t(cs)))
+
+    def reconstruct(self, X):
+        """Y[b] = A X[b] on the device (ss::reconstruct_signal, include/ss/ss.h:79-86)."""
+        X = np.ascontiguousarray(np.atleast_2d(X), dtype=self.dtype)
+        Y = np.empty((X.shape[0], self.shape[0]), dtype=self.dtype)
+        check(getattr(lib(), f"ssb200_reconstruct_batch_{self._sfx}")(
+            self._h, _ptr(X), C.c_size_t(X.shape[0]), C.c_size_t(X.shape[1]), _ptr(Y), C.c_size_t(Y.shape[1])))
+        return Y
+
+
+class Irls(_Solver):
+    _name = "irls"
+
+    def solve(self, b, tolerance=None, max_iterations=100):
+        self._check_signal(b, 1)
+        tol, mi = self._defaults(tolerance, max_iterations)
+        x = np.empty(self.shape[1], dtype=self.dtype)
+        it, err, spd = C.c_uint32(), C.c_double(), C.c_uint8()
+        fn = getattr(lib(), f"ssb200_irls_solve_{self._sfx}")
+        check(fn(self._h, _ptr(b), C.c_ssize_t(b.strides[0] // b.itemsize), tol, mi, _ptr(x), C.c_ssize_t(1),
+                 C.byref(it), C.byref(err), C.byref(spd)))
+        return x, IrlsReport(it.value, err.value, bool(spd.value))
+
+    def solve_batch(self, Y, tolerance=None, max_iterations=100):
+        self._check_signal(Y, 2)
+        if Y.strides[1] != Y.itemsize:
+            Y = np.ascontiguousarray(Y)
+        tol, mi = self._defaults(tolerance, max_iterations)
+        B = Y.shape[0]
+        X = np.empty((B, self.shape[1]), dtype=self.dtype)
+        iters = np.empty(B, dtype=np.uint32)
+        errs = np.empty(B, dtype=np.float64)
+        spd = np.empty(B, dtype=np.uint8)
+        fn = getattr(lib(), f"ssb200_irls_solve_batch_{self._sfx}")
+        check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
+                 _ptr(X), C.c_size_t(X.shape[1]), _ptr(iters), _ptr(errs), _ptr(spd)))
+        return X, iters, errs, spd.astype(bool)
+
+
+def reconstruct_signal(A, x, device=0):
+    """ss::reconstruct_signal (include/ss/ss.h:79-86): y = A x."""
+    return Homotopy(A, device).reconstruct(x)[0]
+
+
+def norm_l1(A, device=0):
+    """ss::norm_l1 (include/ss/ss.h:88-93): divides every column by its l1 norm, in place."""
+    if A.dtype not in _SFX or A.ndim != 2:
+        raise TypeError("A must be a 2-D float32/float64 array")
+    sfx, _ = _SFX[A.dtype]
+    rs, cs = A.strides[0] // A.itemsize, A.strides[1] // A.itemsize
+    check(getattr(lib(), f"ssb200_norm_l1_{sfx}")(_ptr(A), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]),
+                                                   C.c_ssize_t(rs), C.c_ssize_t(cs), C.c_int(device)))
+    return A

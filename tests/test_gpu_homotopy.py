@@ -1,0 +1,234 @@
+"""GPU parity tests of the homotopy path, through the C ABI (sparsesolvers -> libssb200.so):
+  - the committed golden vectors (outputs of the unmodified reference, tests/golden/make_golden.py)
+  - the CPU restatement on seeded inputs, float32 and float64, both contraction kernels
+  - the reference's behavioural tests (src/solvers/test_util.h, bindings/python/tests/test_binding.py)
+  - edge cases and size-independent properties at larger sizes
+"""
+import glob
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+import parity
+from gpu_util import c0_inf, check_homotopy
+
+pytestmark = pytest.mark.gpu
+
+HOMOTOPY_GOLDEN = sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "homotopy_*.npz")))
+
+
+@pytest.fixture(scope="module")
+def ss():
+    import sparsesolvers
+    return sparsesolvers
+
+
+@pytest.mark.parametrize("path", ["simt", "auto"])
+@pytest.mark.parametrize("name", HOMOTOPY_GOLDEN)
+def test_golden(ss, name, path):
+    g = np.load(os.path.join(GOLDEN, name))
+    A = g["A"]
+    if "colmajor" in name:
+        A = np.asfortranarray(A)
+    s = ss.Homotopy(A)
+    s.set_contraction_path(path)
+    check_homotopy(s, g["A"], g["Y"], float(g["tol"]), int(g["max_iter"]), g["X"], g["iters"], g["errs"], name)
+
+
+@pytest.mark.parametrize("path", ["simt", "auto"])
+@pytest.mark.parametrize("dtype,m,n,k,batch", [(np.float32, 128, 512, 10, 300), (np.float64, 128, 512, 10, 200),
+                                               (np.float32, 256, 1024, 16, 256), (np.float32, 504, 1216, 20, 130),
+                                               (np.float64, 100, 230, 7, 70)])
+def test_vs_port(ss, dtype, m, n, k, batch, path):
+    from oracle import port
+    from sparsesolvers import synth
+    A = synth.dictionary(m, n, dtype=dtype, seed=5 + m)
+    Y, _ = synth.sparse_signals(A, batch, k, seed=6 + n)
+    mi = 2 * k + 16
+    Xr, itr, er = port.homotopy(A, Y, 1e-3, mi)
+    s = ss.Homotopy(A)
+    s.set_contraction_path(path)
+    stats, _ = check_homotopy(s, A, Y, 1e-3, mi, Xr, itr, er, f"{np.dtype(dtype).name} {m}x{n} k={k} [{path}]")
+    print(stats, s.counters())
+
+
+def test_single_solve_equals_batch_row(ss):
+    from sparsesolvers import synth
+    A = synth.dictionary(64, 256, dtype=np.float32, seed=1)
+    Y, _ = synth.sparse_signals(A, 5, 4, seed=2)
+    s = ss.Homotopy(A)
+    Xb, itb, eb = s.solve_batch(Y, 1e-3, 30)
+    for b in range(5):
+        x, rep = s.solve(Y[b], 1e-3, 30)
+        assert rep.iter == itb[b]
+        np.testing.assert_allclose(x, Xb[b], rtol=2e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_smoke_identity(ss, dtype):
+    """test_util.h:27-55, test_binding.py:9-20: x == signal exactly, iter == 1, solution_error == 0."""
+    N = 5
+    s = ss.Homotopy(np.eye(N, dtype=dtype))
+    for n in range(N):
+        y = np.zeros(N, dtype=dtype)
+        y[n] = 1
+        x, rep = s.solve(y, 1e-3, N)
+        assert (x == y).all() and rep.iter == 1 and rep.solution_error == 0.0
+
+
+def test_binding_defaults(ss):
+    """test_binding.py:9-20 calls solve(signal) with the default tolerance 10*eps and 100 iterations."""
+    for dtype in (np.float32, np.float64):
+        s = ss.Homotopy(np.identity(10, dtype=dtype))
+        y = np.zeros(10, dtype=dtype)
+        y[3] = 1
+        x, rep = s.solve(y)
+        assert (x == y).all() and rep.iter == 1 and rep.solution_error == 0
+
+
+def test_strided_views(ss):
+    """test_util.h:57-92 and test_binding.py:31-68: column-subset, row-subset and transposed views."""
+    buf = np.zeros((5, 10), dtype=np.float32)
+    buf[:, 5:] = np.eye(5, dtype=np.float32)
+    s = ss.Homotopy(buf[:, 5:])
+    for n in range(5):
+        y = np.zeros(5, dtype=np.float32)
+        y[n] = 1
+        x, _ = s.solve(y, 1e-3, 5)
+        assert (x == y).all()
+    big = np.zeros((20, 10), dtype=np.float64)
+    big[::2, :] = np.eye(10)
+    s = ss.Homotopy(big[::2, :])
+    y = np.zeros(10)
+    y[7] = 1
+    x, rep = s.solve(y)
+    assert (x == y).all() and rep.iter == 1
+    T = np.triu(np.ones((6, 6), dtype=np.float32)) / 6
+    st, sc = ss.Homotopy(T.T), ss.Homotopy(np.ascontiguousarray(T.T))
+    y = T.T[:, 2].copy()
+    xa, ra = st.solve(y, 1e-3, 12)
+    xb, rb = sc.solve(y, 1e-3, 12)
+    assert ra.iter == rb.iter and np.array_equal(xa, xb)
+    # a strided signal view
+    y2 = np.zeros(20)
+    y2[::2][7] = 1
+    x, rep = s.solve(y2[::2])
+    assert x[7] == 1 and rep.iter == 1
+
+
+def test_noisy_signal(ss):
+    """test_util.h:94-126"""
+    rng = np.random.default_rng(0)
+    N = 50
+    s = ss.Homotopy(np.eye(N, dtype=np.float32))
+    for n in range(0, N, 7):
+        y = rng.uniform(0, 0.01, size=N).astype(np.float32)
+        y[n] += 1
+        x, rep = s.solve(y, 0.01, N)
+        assert (x > 0.01).sum() == 1 and np.argmax(x) == n
+        assert 1 <= rep.iter <= N and (rep.iter == N or rep.solution_error <= 0.01)
+
+
+@pytest.mark.parametrize("shape,dtype", [((10, 10), np.float32), ((25, 10), np.float32), ((10, 25), np.float32),
+                                         ((10, 25), np.float64)])
+def test_permutations(ss, shape, dtype):
+    """test_util.h:204-257 (homotopy_test.cpp:48-61)"""
+    M, N = shape
+    rng = np.random.default_rng(0)
+    perms = itertools.permutations(range(1, M + 1))
+    A = np.stack([np.array(next(perms), dtype=np.float64) for _ in range(N)], axis=1)
+    A /= np.abs(A).sum(axis=0, keepdims=True)
+    A = A.astype(dtype)
+    s = ss.Homotopy(A)
+    Y = (A.T.astype(np.float64) + rng.standard_normal((N, M)) * 1e-4).astype(dtype)
+    X, it, err = s.solve_batch(Y, 1e-3, N)
+    assert (np.argmax(X, axis=1) == np.arange(N)).all()
+
+
+@pytest.mark.parametrize("shape", [(100, 25), (25, 100)])
+def test_noisy_patterns(ss, shape):
+    """test_util.h:136-197: a patterned needle in an l1-normalised Gaussian haystack; reconstruction within 5*ERROR."""
+    M, N = shape
+    ERROR = 0.05
+    rng = np.random.default_rng(0)
+    for n in range(0, N, max(1, N // 5)):
+        A = rng.normal(0.5, 0.1, size=(M, N)).astype(np.float32)
+        A[::2, n] += 0.5
+        ss.norm_l1(A)
+        np.testing.assert_allclose(np.abs(A).sum(axis=0), 1, rtol=1e-5)
+        y = A[:, n].copy()
+        s = ss.Homotopy(A)
+        x, rep = s.solve(y, ERROR / 10, N)
+        assert np.argmax(x) == n
+        yr = ss.reconstruct_signal(A, x)
+        assert np.abs(yr - y).max() < 5 * ERROR
+
+
+def test_quirk_sign_init(ss):
+    """homotopy-cpu.cpp:223-227: d0 = sign(|c|) -- un-normalised signals follow the reference's own path."""
+    g = np.load(os.path.join(GOLDEN, "homotopy_f64_quirk_64x256_k8.npz"))
+    s = ss.Homotopy(g["A"])
+    X, it, err = s.solve_batch(g["Y"], float(g["tol"]), int(g["max_iter"]))
+    assert (it == g["iters"]).all()
+    np.testing.assert_allclose(X, g["X"], rtol=1e-8, atol=1e-10 * np.abs(g["X"]).max())
+
+
+def test_edge_cases(ss):
+    from oracle import port
+    from sparsesolvers import synth
+    A = synth.dictionary(48, 100, dtype=np.float32, seed=8)     # N, M not multiples of the tile sizes
+    s = ss.Homotopy(A)
+    X, it, err = s.solve_batch(np.zeros((0, 48), dtype=np.float32), 1e-3, 10)      # empty batch
+    assert X.shape == (0, 100) and it.shape == (0,)
+    Y, _ = synth.sparse_signals(A, 7, 3, seed=9)
+    Y[3] = 0                                                     # an all-zero signal
+    Xr, itr, er = port.homotopy(A, Y, 1e-3, 20)
+    Xg, itg, eg = s.solve_batch(Y, 1e-3, 20)
+    assert (itg == itr).all()
+    assert itg[3] == 1 and not Xg[3].any()
+    # max_iter = 1 and max_iter > N
+    for mi in (1, 150):
+        Xr, itr, er = port.homotopy(A, Y[:3], 1e-3, mi)
+        Xg, itg, eg = s.solve_batch(Y[:3], 1e-3, mi)
+        assert (itg == itr).all()
+        np.testing.assert_allclose(Xg, Xr, rtol=1e-3, atol=1e-5)
+    with pytest.raises(TypeError):
+        s.solve(Y[0].astype(np.float64))                         # noconvert, binding.cpp:108
+    with pytest.raises(ValueError):
+        s.solve(np.zeros(5, dtype=np.float32))
+
+
+def test_refresh(ss):
+    """the reference's non-owning view lets callers edit A between solves (homotopy_bench.cpp:38-48)."""
+    A = np.eye(6, dtype=np.float32)
+    s = ss.Homotopy(A)
+    y = np.zeros(6, dtype=np.float32); y[2] = 1
+    A2 = 2 * A
+    s.refresh(A2)
+    x, rep = s.solve(y, 1e-3, 6)
+    assert x[2] == 0.5 and rep.iter == 1
+
+
+def test_full_size_properties(ss):
+    """C2 shape (512x2048, k=32) on a batch too large for the CPU oracle in test time: size-independent properties.
+    Converged signals reconstruct y, recover the planted support, and take k..k+4 iterations."""
+    from sparsesolvers import synth
+    A = synth.dictionary(512, 2048, dtype=np.float32, seed=1234 + 2)
+    Y, X0 = synth.sparse_signals(A, 4096, 32, seed=99)
+    s = ss.Homotopy(A)
+    X, it, err = s.solve_batch(Y, 1e-3, 80)
+    conv = it < 80
+    assert conv.mean() > 0.995
+    assert (err[conv] <= 1e-3).all()
+    assert it[conv].min() >= 32 and it[conv].max() <= 40
+    sup = parity.support(X, 1e-5)
+    assert ((sup == (X0 != 0)).all(axis=1))[conv].mean() > 0.995
+    R = Y - s.reconstruct(X)
+    assert np.abs(R[conv]).max() < 5e-3
+    # idempotence of the batch split: the same signals in a different batch composition give the same answers
+    X2, it2, _ = s.solve_batch(Y[1000:1100], 1e-3, 80)
+    assert (it2 == it[1000:1100]).all()
+    np.testing.assert_array_equal(X2, X[1000:1100])
