@@ -8,7 +8,7 @@
  * do their arithmetic through the OpenBLAS wrapper (src/linalg/blas_wrapper.h:99-400).  The entry
  * points below replace that dispatch + BLAS layer for this path: a maintainer re-implements the four
  * overloads as calls into this header (INTEGRATION.md shows the stub) and nothing above
- * include/ss/*.h changes.
+ * the include/ss headers changes.
  *
  * Conventions
  *   - plain pointers and sizes only; no C++ / torch types cross the boundary.
@@ -156,6 +156,11 @@ int ssb200_get_counters(void* handle, uint64_t counters[4]);
 int ssb200_set_timing(void* handle, int enabled);
 int ssb200_get_timing(void* handle, double ms[2]);
 int ssb200_set_contraction_path(void* handle, int path);
+/* test / bench hook for the contraction kernel alone: Q[r][n] = sum_m A[m][n] * P[r][m] for `rows` host rows
+ * (P: rows x M, Q: rows x N, both dense row-major), computed by path 1 (SIMT) or 2 (tcgen05, float32);
+ * *ms_per_launch = mean device time of `reps` back-to-back launches (CUDA events on the handle's stream). */
+int ssb200_debug_contract_f32(void* handle, const float* P, size_t rows, float* Q, int path, int reps, double* ms_per_launch);
+int ssb200_debug_contract_f64(void* handle, const double* P, size_t rows, double* Q, int path, int reps, double* ms_per_launch);
 
 #ifdef __cplusplus
 }

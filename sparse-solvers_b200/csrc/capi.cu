@@ -214,6 +214,9 @@ int ssb200_homotopy_solve_batch_dev_##SFX(void* h, const T* Y, size_t batch, siz
 int ssb200_reconstruct_batch_##SFX(void* h, const T* X, size_t batch, size_t ldx, T* Y, size_t ldy)                     \
 { return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (X && Y), "null pointer");                \
                        device_guard g(s->device); s->reconstruct_host(X, batch, ldx, Y, ldy); }); }                     \
+int ssb200_debug_contract_##SFX(void* h, const T* P, size_t rows, T* Q, int path, int reps, double* ms_per_launch)      \
+{ return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(P && Q, "null pointer"); device_guard g(s->device);     \
+                       double ms = s->debug_contract(P, rows, Q, path, reps); if (ms_per_launch) *ms_per_launch = ms; }); } \
 int ssb200_norm_l1_##SFX(T* A, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs, int device)                              \
 { return norm_l1<T>(A, m, n, rs, cs, device); }
 

@@ -1,9 +1,289 @@
-// placeholder until the tcgen05 kernel lands (replaced in the next commit)
+// Batched residual correlation on the 5th-generation tensor cores (sm_100a):
+//     Q[r][n] = sum_m At[n][m] * P[r][m]        (the reference's x gemv(A^T, .) calls, homotopy-cpu.cpp:97,:120,
+//                                                batched over signals: one dense A^T . P contraction)
+// float32 accuracy comes from the 3xTF32 split  a*p ~= a_lo*p_hi + a_hi*p_lo + a_hi*p_hi  with
+// hi = rna_tf32(v), lo = rna_tf32(v - hi): three tcgen05.mma.kind::tf32 per K-step into one fp32 TMEM accumulator.
+//
+// Kernel shape (persistent, one CTA per SM, 192 threads):
+//   warp 0      TMA producer: per K-block (32 floats = one 128-byte swizzle span) loads four tiles
+//               A_hi, A_lo [128 atoms x 32] and P_hi, P_lo [256 signals x 32] (cp.async.bulk.tensor.2d, SWIZZLE_128B)
+//   warp 1      MMA issuer (one lane): UMMA M=128 (atoms) x N=256 (signals) x K=8, accumulator in TMEM;
+//               two accumulators (2 x 256 columns) so tile i+1's main loop overlaps tile i's epilogue
+//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> Q; lane = atom, so every
+//               store instruction writes 128 contiguous bytes of one signal's row
+// Barriers: full/empty per smem stage (TMA <-> MMA), tmem_full/tmem_empty per accumulator (MMA <-> epilogue).
+#include <cuda.h>
+
+#include <mutex>
+
 #include "solver_base.h"
+
 namespace ssb {
-struct TcPlan {};
-TcPlan* tc_plan_create(const float*, const float*, int, int, const float*, const float*, int) { return nullptr; }
-void tc_plan_destroy(TcPlan*) {}
-void tc_contract(TcPlan*, int, float*, int, cudaStream_t) { throw invalid_argument{ "tcgen05 contraction not built" }; }
-bool tc_supported(int, int) { return false; }
+
+namespace {
+
+constexpr int TILE_ATOMS = 128;     // UMMA M
+constexpr int TILE_SIGS = 256;      // UMMA N
+constexpr int BLOCK_K = 32;         // floats per K-block = 128 bytes
+constexpr int UMMA_K = 8;           // tf32
+constexpr int STAGES = 2;
+constexpr int A_TILE_BYTES = TILE_ATOMS * BLOCK_K * 4;   // 16 KB
+constexpr int P_TILE_BYTES = TILE_SIGS * BLOCK_K * 4;    // 32 KB
+constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * P_TILE_BYTES;   // 96 KB
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;  // + alignment slack
+constexpr int TMEM_COLS = 512;
+constexpr int THREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// K-major operand tile, rows of 128 bytes, SWIZZLE_128B: 8-row groups are 1024 bytes apart
+__device__ __forceinline__ uint64_t make_desc(const void* tile) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_u32(tile) >> 4) & 0x3FFF);   // start address
+    d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset
+    d |= (uint64_t)1 << 46;                            // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
+    return d;
+}
+
+// instruction descriptor: D = F32, A = B = TF32, both K-major, M = 128, N = 256
+constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TILE_SIGS >> 3) << 17) | ((uint32_t)(TILE_ATOMS >> 4) << 24);
+
+__global__ void __launch_bounds__(THREADS, 1)
+contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                       const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
+                       float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar[2], tmem_empty_bar[2];
+    __shared__ uint32_t tmem_base_slot;
+
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_tiles = atom_tiles * sig_tiles;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int n0 = (tile % atom_tiles) * TILE_ATOMS;
+                const int r0 = (tile / atom_tiles) * TILE_SIGS;
+                for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    tma_load_2d(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
+                    tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
+                    tma_load_2d(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
+                    tma_load_2d(st + 2 * A_TILE_BYTES + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            uint32_t it = 0, t = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+                const int acc = t & 1;
+                mbar_wait(&tmem_empty_bar[acc], ((t >> 1) & 1) ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + (uint32_t)acc * TILE_SIGS;
+                for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                    const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + A_TILE_BYTES);
+                    const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + P_TILE_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+                        const uint64_t adv = (uint64_t)((kk * UMMA_K * 4) >> 4);   // bytes along K inside the swizzle span
+                        umma_tf32(d_tmem, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                        umma_tf32(d_tmem, a_hi + adv, p_lo + adv, IDESC, 1);
+                        umma_tf32(d_tmem, a_hi + adv, p_hi + adv, IDESC, 1);
+                    }
+                    umma_commit(&empty_bar[s]);            // frees the smem stage when these MMAs retire
+                }
+                umma_commit(&tmem_full_bar[acc]);          // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue: TMEM -> registers -> Q =====
+        const int quarter = warp & 3;                      // TMEM lanes this warp may read
+        uint32_t t = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            const int acc = t & 1;
+            const int n0 = (tile % atom_tiles) * TILE_ATOMS;
+            const int r0 = (tile / atom_tiles) * TILE_SIGS;
+            mbar_wait(&tmem_full_bar[acc], (t >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * TILE_SIGS;
+            float* qcol = Q + n0 + quarter * 32 + lane;
+#pragma unroll 1
+            for (int c0 = 0; c0 < TILE_SIGS; c0 += 32) {
+                if (r0 + c0 >= rows) break;                // warp-uniform
+                uint32_t v[32];
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr0 + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int r = r0 + c0 + j;
+                    if (r < rows) qcol[(size_t)r * ldq] = __uint_as_float(v[j]);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    }
+}
+
+// ---- TMA descriptors through the driver entry point (no link-time libcuda dependency) -------------------
+using encode_fn_t = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_fn_t get_encode()
+{
+    static encode_fn_t fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<encode_fn_t>(p);
+    });
+    return fn;
+}
+
+CUtensorMap make_map(const float* base, int inner, int outer, int box_rows)
+{
+    encode_fn_t enc = get_encode();
+    if (!enc) throw invalid_argument{ "cuTensorMapEncodeTiled is not available from this driver" };
+    CUtensorMap m;
+    cuuint64_t dims[2] = { (cuuint64_t)inner, (cuuint64_t)outer };
+    cuuint64_t strides[1] = { (cuuint64_t)inner * sizeof(float) };
+    cuuint32_t box[2] = { (cuuint32_t)BLOCK_K, (cuuint32_t)box_rows };
+    cuuint32_t estr[2] = { 1, 1 };
+    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw invalid_argument{ "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")" };
+    return m;
+}
+
+}  // namespace
+
+struct TcPlan {
+    CUtensorMap a_hi, a_lo, p_hi, p_lo;
+    int n_pad, mp, rows_alloc, sms;
+};
+
+bool tc_supported(int n_pad, int mp) { return n_pad % TILE_ATOMS == 0 && mp % BLOCK_K == 0 && get_encode() != nullptr; }
+
+TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp, const float* P_hi, const float* P_lo, int rows_alloc)
+{
+    SSB_REQUIRE(rows_alloc % TILE_SIGS == 0, "P buffers must be allocated in multiples of 256 rows");
+    auto* p = new TcPlan;
+    try {
+        p->a_hi = make_map(At_hi, mp, n_pad, TILE_ATOMS);
+        p->a_lo = make_map(At_lo, mp, n_pad, TILE_ATOMS);
+        p->p_hi = make_map(P_hi, mp, rows_alloc, TILE_SIGS);
+        p->p_lo = make_map(P_lo, mp, rows_alloc, TILE_SIGS);
+    } catch (...) { delete p; throw; }
+    p->n_pad = n_pad; p->mp = mp; p->rows_alloc = rows_alloc;
+    int dev = 0;
+    SSB_CUDA(cudaGetDevice(&dev));
+    SSB_CUDA(cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, dev));
+    SSB_CUDA(cudaFuncSetAttribute(contract_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    return p;
+}
+
+void tc_plan_destroy(TcPlan* p) { delete p; }
+
+void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
+{
+    if (rows <= 0) return;
+    SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
+    const int atom_tiles = p->n_pad / TILE_ATOMS;
+    const int sig_tiles = (rows + TILE_SIGS - 1) / TILE_SIGS;
+    const int grid = std::min(atom_tiles * sig_tiles, p->sms);
+    contract_tf32x3_kernel<<<grid, THREADS, SMEM_BYTES, stream>>>(p->a_hi, p->a_lo, p->p_hi, p->p_lo, Q, ldq, rows,
+                                                                  atom_tiles, sig_tiles, p->mp / BLOCK_K);
+    SSB_CUDA(cudaGetLastError());
+}
+
+}  // namespace ssb

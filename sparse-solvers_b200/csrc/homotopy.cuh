@@ -92,6 +92,9 @@ public:
     void solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* X, size_t ldx,
                           uint32_t* iters, double* errs);
     void reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, size_t ldy);
+    // test / bench hook: Q[r][n] = sum_m A[m][n] P[r][m] through the chosen contraction kernel, `reps` launches;
+    // returns the mean device time per launch in ms
+    double debug_contract(const T* P, size_t rows, T* Q, int path, int reps);
 
 private:
     dev_buffer At_, At_hi_, At_lo_, G_;

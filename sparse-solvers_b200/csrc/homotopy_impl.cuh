@@ -133,8 +133,8 @@ void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, 
 {
     SSB_REQUIRE(M > 0, "no dictionary");
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");   // homotopy-cpu.cpp:199
-    SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     if (batch == 0) return;
+    SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     if (!st) st = stream;
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     const size_t chunk = choose_chunk(batch, kmax);
@@ -151,8 +151,8 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
 {
     SSB_REQUIRE(M > 0, "no dictionary");
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");
-    SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     if (batch == 0) return;
+    SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     const size_t chunk = choose_chunk(batch, kmax);
     reserve_workspace(chunk, kmax);
@@ -172,6 +172,34 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         SSB_CUDA(cudaMemcpyAsync(errs + b0, stErr_.p, rows * sizeof(double), cudaMemcpyDeviceToHost, stream));
         SSB_CUDA(cudaStreamSynchronize(stream));
     }
+}
+
+template <typename T>
+double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int reps)
+{
+    SSB_REQUIRE(M > 0 && rows > 0 && reps > 0, "bad arguments");
+    reserve_workspace(rows, 2);
+    const bool tc = path == 2;
+    SSB_REQUIRE(!tc || (sizeof(T) == 4 && tc_supported(Npad, Mp)), "tcgen05 contraction unavailable for this dtype/shape");
+    dev_buffer dP;
+    dP.reserve(rows * M * sizeof(T));
+    SSB_CUDA(cudaMemcpyAsync(dP.p, P, rows * M * sizeof(T), cudaMemcpyHostToDevice, stream));
+    const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
+    stage_signals_kernel<T><<<blocks, 256, 0, stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, P_[0].template as<T>(),
+                                                       tc ? Plo_[0].template as<T>() : nullptr, Mp, tc ? 1 : 0);
+    SSB_CUDA(cudaGetLastError());
+    contract(tc, 0, rows, stream);   // warm-up + the result
+    cudaEvent_t e0 = get_event(), e1 = get_event();
+    SSB_CUDA(cudaEventRecord(e0, stream));
+    for (int i = 0; i < reps; ++i) contract(tc, 0, rows, stream);
+    SSB_CUDA(cudaEventRecord(e1, stream));
+    SSB_CUDA(cudaMemcpy2DAsync(Q, N * sizeof(T), Q_.p, Npad * sizeof(T), N * sizeof(T), rows, cudaMemcpyDeviceToHost, stream));
+    SSB_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0.f;
+    SSB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    event_pool.push_back(e0); event_pool.push_back(e1);
+    collect_spans();
+    return (double)ms / reps;
 }
 
 template <typename T>

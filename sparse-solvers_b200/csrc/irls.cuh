@@ -116,8 +116,8 @@ public:
     {
         SSB_REQUIRE(M > 0, "no dictionary");
         SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");
-        SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
         if (batch == 0) return;
+        SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
         if (!st) st = stream;
         if (wide) {
             // what the reference build returns for M < N: no iteration, SPD failure, x = 0/0

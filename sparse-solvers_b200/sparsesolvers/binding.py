@@ -151,6 +151,16 @@ class Homotopy(_Solver):
             check(fn(self._h, C.c_void_p(y_ptr), C.c_size_t(batch), C.c_size_t(ldy), tol, mi, C.c_void_p(x_ptr),
                      C.c_size_t(ldx), C.c_void_p(iters_ptr), C.c_void_p(errs_ptr)))
 
+    def debug_contract(self, P, path="simt", reps=1):
+        """Test/bench hook: Q[r] = A^T P[r] through one contraction kernel; returns (Q, ms per launch)."""
+        P = np.ascontiguousarray(P, dtype=self.dtype)
+        Q = np.empty((P.shape[0], self.shape[1]), dtype=self.dtype)
+        ms = C.c_double()
+        check(getattr(lib(), f"ssb200_debug_contract_{self._sfx}")(
+            self._h, _ptr(P), C.c_size_t(P.shape[0]), _ptr(Q), C.c_int({"simt": 1, "tcgen05": 2}[path]), C.c_int(reps),
+            C.byref(ms)))
+        return Q, ms.value
+
     def refresh(self, A):
         """Re-uploads an edited dictionary of the same shape (the reference state is a non-owning view,
         include/ss/policies.h:42; its bench edits A in place between solves, homotopy_bench.cpp:38-48)."""

@@ -1,0 +1,49 @@
+"""The residual-correlation contraction Q = A^T P alone: both kernels against float64 numpy."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ss():
+    import sparsesolvers
+    return sparsesolvers
+
+
+def _rel_err(Q, A, P):
+    ref = P.astype(np.float64) @ A.astype(np.float64)
+    scale = np.abs(P.astype(np.float64)) @ np.abs(A.astype(np.float64))   # sum |a||p|: the rounding scale
+    return (np.abs(Q - ref) / scale).max()
+
+
+@pytest.mark.parametrize("m,n,rows", [(512, 2048, 1), (512, 2048, 3), (512, 2048, 300), (504, 1216, 77), (96, 160, 40)])
+def test_simt_f32(ss, m, n, rows):
+    rng = np.random.default_rng(m + rows)
+    A = (rng.standard_normal((m, n)) / np.sqrt(m)).astype(np.float32)
+    P = rng.standard_normal((rows, m)).astype(np.float32)
+    Q, _ = ss.Homotopy(A).debug_contract(P, "simt")
+    assert _rel_err(Q, A, P) < 5e-7
+
+
+@pytest.mark.parametrize("m,n,rows", [(512, 2048, 256), (512, 2048, 1000), (504, 1216, 77), (96, 160, 40), (4096, 1024, 513)])
+def test_tcgen05_3xtf32(ss, m, n, rows):
+    """3xTF32 must stay at float32 level: the error is measured against sum |a||p| and held to a few fp32 ulps."""
+    rng = np.random.default_rng(m + rows)
+    A = (rng.standard_normal((m, n)) / np.sqrt(m)).astype(np.float32)
+    P = (rng.standard_normal((rows, m)) * np.exp(rng.uniform(-3, 3, size=(rows, 1)))).astype(np.float32)
+    s = ss.Homotopy(A)
+    Q, _ = s.debug_contract(P, "tcgen05")
+    Qs, _ = s.debug_contract(P, "simt")
+    assert np.isfinite(Q).all()
+    e_tc, e_simt = _rel_err(Q, A, P), _rel_err(Qs, A, P)
+    print(f"rel err tcgen05 {e_tc:.3g} simt {e_simt:.3g}")
+    assert e_tc < 2e-6
+
+
+def test_f64(ss):
+    rng = np.random.default_rng(0)
+    A = rng.standard_normal((200, 300)) / np.sqrt(200)
+    P = rng.standard_normal((50, 200))
+    Q, _ = ss.Homotopy(A).debug_contract(P, "simt")
+    assert _rel_err(Q, A, P) < 1e-15
