@@ -1,17 +1,21 @@
 // Batched residual correlation on the 5th-generation tensor cores (sm_100a):
 //     Q[r][n] = sum_m At[n][m] * P[r][m]        (the reference's x gemv(A^T, .) calls, homotopy-cpu.cpp:97,:120,
 //                                                batched over signals: one dense A^T . P contraction)
-// float32 accuracy comes from the 3xTF32 split  a*p ~= a_lo*p_hi + a_hi*p_lo + a_hi*p_hi  with
-// hi = rna_tf32(v), lo = rna_tf32(v - hi): three tcgen05.mma.kind::tf32 per K-step into one fp32 TMEM accumulator.
+// float32 accuracy comes from the 3xTF32 split  a*p ~= a_hi*p_hi + (a_lo*p_hi + a_hi*p_lo)  with
+// hi = rna_tf32(v), lo = rna_tf32(v - hi): three tcgen05.mma.kind::tf32 per K-step.  The tensor core adds
+// into its fp32 accumulator with round-toward-zero, a bias that grows with the number of accumulation
+// events (measured: -2.5e-6 relative with all three products in one accumulator at M = 512, gpurun_out/
+// r1_contract_c2.json).  The two small correction products therefore get their OWN accumulator and are
+// added once, round-to-nearest, in the epilogue: the main accumulator sees one event per K-step instead of 3.
 //
 // Kernel shape (persistent, one CTA per SM, 192 threads):
 //   warp 0      TMA producer: per K-block (32 floats = one 128-byte swizzle span) loads four tiles
 //               A_hi, A_lo [128 atoms x 32] and P_hi, P_lo [256 signals x 32] (cp.async.bulk.tensor.2d, SWIZZLE_128B)
-//   warp 1      MMA issuer (one lane): UMMA M=128 (atoms) x N=256 (signals) x K=8, accumulator in TMEM;
-//               two accumulators (2 x 256 columns) so tile i+1's main loop overlaps tile i's epilogue
-//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> Q; lane = atom, so every
-//               store instruction writes 128 contiguous bytes of one signal's row
-// Barriers: full/empty per smem stage (TMA <-> MMA), tmem_full/tmem_empty per accumulator (MMA <-> epilogue).
+//   warp 1      MMA issuer (one lane): UMMA M=128 (atoms) x N=256 (signals) x K=8; TMEM columns [0,256) hold
+//               the main accumulator, [256,512) the correction accumulator (all 512 columns of the SM)
+//   warps 2..9  epilogue: tcgen05.ld 32 lanes x 32 columns of both accumulators -> registers -> add -> Q;
+//               lane = atom, so every store instruction writes 128 contiguous bytes of one signal's row
+// Barriers: full/empty per smem stage (TMA <-> MMA), tmem_full/tmem_empty for the accumulator pair (MMA <-> epilogue).
 #include <cuda.h>
 
 #include <mutex>
@@ -32,7 +36,8 @@ constexpr int P_TILE_BYTES = TILE_SIGS * BLOCK_K * 4;    // 32 KB
 constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * P_TILE_BYTES;   // 96 KB
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;  // + alignment slack
 constexpr int TMEM_COLS = 512;
-constexpr int THREADS = 192;
+constexpr int EPI_WARPS = 8;
+constexpr int THREADS = 64 + 32 * EPI_WARPS;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -76,6 +81,18 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+
 // K-major operand tile, rows of 128 bytes, SWIZZLE_128B: 8-row groups are 1024 bytes apart
 __device__ __forceinline__ uint64_t make_desc(const void* tile) {
     uint64_t d = 0;
@@ -95,7 +112,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
                        float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks)
 {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar[2], tmem_empty_bar[2];
+    __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
 
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -104,7 +121,8 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full_bar[a], 1); mbar_init(&tmem_empty_bar[a], 4); }
+        mbar_init(&tmem_full_bar, 1);
+        mbar_init(&tmem_empty_bar, EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -140,11 +158,10 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         // ===== MMA issuer =====
         if (lane == 0) {
             uint32_t it = 0, t = 0;
+            const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-                const int acc = t & 1;
-                mbar_wait(&tmem_empty_bar[acc], ((t >> 1) & 1) ^ 1);
+                mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t d_tmem = tmem_base + (uint32_t)acc * TILE_SIGS;
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
                     const int s = it % STAGES;
                     mbar_wait(&full_bar[s], (it / STAGES) & 1);
@@ -155,50 +172,43 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 #pragma unroll
                     for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
                         const uint64_t adv = (uint64_t)((kk * UMMA_K * 4) >> 4);   // bytes along K inside the swizzle span
-                        umma_tf32(d_tmem, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
-                        umma_tf32(d_tmem, a_hi + adv, p_lo + adv, IDESC, 1);
-                        umma_tf32(d_tmem, a_hi + adv, p_hi + adv, IDESC, 1);
+                        umma_tf32(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                        umma_tf32(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
+                        umma_tf32(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
                     }
                     umma_commit(&empty_bar[s]);            // frees the smem stage when these MMAs retire
                 }
-                umma_commit(&tmem_full_bar[acc]);          // accumulator complete
+                umma_commit(&tmem_full_bar);               // both accumulators complete
             }
         }
     } else {
         // ===== epilogue: TMEM -> registers -> Q =====
         const int quarter = warp & 3;                      // TMEM lanes this warp may read
+        const int half = (warp - 2) >> 2;                  // which 128 signal columns of the tile
         uint32_t t = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-            const int acc = t & 1;
             const int n0 = (tile % atom_tiles) * TILE_ATOMS;
-            const int r0 = (tile / atom_tiles) * TILE_SIGS;
-            mbar_wait(&tmem_full_bar[acc], (t >> 1) & 1);
+            const int r0 = (tile / atom_tiles) * TILE_SIGS + half * (TILE_SIGS / 2);
+            mbar_wait(&tmem_full_bar, t & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * TILE_SIGS;
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
             float* qcol = Q + n0 + quarter * 32 + lane;
 #pragma unroll 1
-            for (int c0 = 0; c0 < TILE_SIGS; c0 += 32) {
+            for (int c0 = 0; c0 < TILE_SIGS / 2; c0 += 32) {
                 if (r0 + c0 >= rows) break;                // warp-uniform
-                uint32_t v[32];
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                    : "r"(taddr0 + (uint32_t)c0));
+                uint32_t v[32], w[32];
+                tmem_ld32(taddr0 + (uint32_t)c0, v);
+                tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int r = r0 + c0 + j;
-                    if (r < rows) qcol[(size_t)r * ldq] = __uint_as_float(v[j]);
+                    if (r < rows) qcol[(size_t)r * ldq] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
                 }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            if (lane == 0) mbar_arrive(&tmem_empty_bar);
         }
     }
 

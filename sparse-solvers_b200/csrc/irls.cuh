@@ -153,7 +153,7 @@ public:
             end_span(span, st);
             counters[1]++; counters[2] += rows;
             IrlsArgs<T> a{};
-            a.N = N; a.lde = Npad; a.E = E_.as<T>(); a.Rc = Rc_.as<T>(); a.S = S_.as<T>();
+            a.N = N; a.lde = Npad; a.E = E_.as<T>(); a.Qt = Qt_.as<T>(); a.M = M; a.ldq = Mp; a.Rc = Rc_.as<T>(); a.S = S_.as<T>();
             a.X = dX + b0 * ldx; a.ldx = ldx; a.L = L_.as<T>(); a.vec = vec_.as<T>();
             a.iters = d_iters + b0; a.errs = d_errs + b0; a.spd = d_spd + b0;
             a.tol = tol; a.max_iter = max_iter;

@@ -5,11 +5,12 @@
 //
 // With A = QR (thin, M >= N) the reference forms, every iteration,
 //     G = Q^T (Q o w),  L = chol(tril(G)),  s = L^-T L^-1 (Q^T y),  x = R^-1 Q^T (Q s).
-// Here Q^T y comes from one batched contraction, and E = Q^T Q (computed once per dictionary, with
-// its rounding-level off-diagonals kept) gives G_ij = E_ij * w_j and Q^T (Q s) = E s: the same
-// numbers up to summation order, N^2 instead of M N^2 work per iteration.  The SPD test
-// (sqrt(pivot) <= eps, cholesky_decomposition.h:80-83) is evaluated on that G, because it is how
-// most solves end.
+// Q^T y comes from one batched contraction and Q^T (Q s) = E s with E = Q^T Q computed once.
+// G is formed the reference's way -- column j of Q scaled by w_j first, then the dot products over
+// the M rows in order, multiply and add rounded separately -- because the way most solves END depends
+// on it: the last pivots are w_j minus rounding-level terms, and whether sqrt(pivot) comes out
+// <= eps ("not SPD", cholesky_decomposition.h:80-83) or NaN (which passes that test) is decided by
+// those roundings.  A cheaper G_ij = E_ij * w_j flips that outcome on ~10 % of signals (measured).
 #pragma once
 
 #include "common.cuh"
@@ -21,6 +22,8 @@ struct IrlsArgs {
     int N;              // columns of A
     int lde;            // leading dimension of E and S (= Npad)
     const T* E;         // [N][lde]   Q^T Q
+    const T* Qt;        // [Npad][ldq] columns of Q, contiguous
+    int M, ldq;
     const T* Rc;        // [N][N]     R stored column-major: Rc[i*N + k] = R[k][i]
     const T* S;         // [rows][lde] Q^T y
     T* X; size_t ldx;   // output
@@ -29,6 +32,12 @@ struct IrlsArgs {
     uint32_t* iters; double* errs; uint8_t* spd;
     T tol; uint32_t max_iter;
 };
+
+// separately rounded multiply / add: keeps nvcc from contracting them into an FMA the reference's build does not use
+__device__ __forceinline__ float  mul_rn(float a, float b)   { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float  add_rn(float a, float b)   { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
 
 template <typename T, int THREADS>
 __device__ __forceinline__ T block_sum(T v, T* red) {
@@ -71,14 +80,18 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
     __syncthreads();
 
     do {
-        // ---- irls_newton (:39-60).  G_ij = E_ij w_j on the lower triangle, left-looking Cholesky.
+        // ---- irls_newton (:39-60).  G = Q^T (Q o w) on the lower triangle (:47-48), left-looking Cholesky.
         int bad = 0;
         for (int j = 0; j < N; ++j) {
             const T wj = w[j];
+            const T* qj = a.Qt + (size_t)j * a.ldq;
             for (int i = j + tid; i < N; i += THREADS) {
+                const T* qi = a.Qt + (size_t)i * a.ldq;
+                T g = T(0);
+                for (int m = 0; m < a.M; ++m) g = add_rn(g, mul_rn(qi[m], mul_rn(qj[m], wj)));
                 T acc = T(0);
-                for (int k = 0; k < j; ++k) acc += L[(size_t)k * N + i] * L[(size_t)k * N + j];
-                L[(size_t)j * N + i] = a.E[(size_t)i * a.lde + j] * wj - acc;
+                for (int k = 0; k < j; ++k) acc = add_rn(acc, mul_rn(L[(size_t)k * N + i], L[(size_t)k * N + j]));
+                L[(size_t)j * N + i] = g - acc;
             }
             __syncthreads();
             const T ajj = sqrt(L[(size_t)j * N + j]);
@@ -132,6 +145,11 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
         __syncthreads();
         mx = red[0];
         for (int q = 1; q < NW; ++q) mx = max(mx, red[q]);
+        // a NaN pivot (sqrt of a negative rounding-level pivot passes the SPD test) turns every entry into NaN;
+        // the reference's running max / nth_element then carry the NaN of entry 0 through (irls-cpu.cpp:100,:107)
+        const T xn0 = xn[0];
+        const bool all_nan = xn0 != xn0;
+        if (all_nan) mx = xn0;
         abstol = mx * a.tol;
         __syncthreads();
         T top = -num_traits<T>::max(), sec = -num_traits<T>::max();
@@ -159,6 +177,7 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
             top = nt;
         }
         second = (N > 1) ? sec : top;
+        if (all_nan) second = xn0;
         if (second / (T)N < eps) eps = second / (T)N;                 // :110
         __syncthreads();
         T sw = T(0);
