@@ -1,0 +1,57 @@
+"""Summarises an .ncu-rep (ncu --set full) into text: per-launch headline metrics + the SASS lines with most stall samples.
+    python tools/ncu_summary.py gpurun_out/prof.ncu-rep > profiles/xxx.txt"""
+import csv
+import io
+import subprocess
+import sys
+
+rep = sys.argv[1]
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "sm__cycles_elapsed.max",
+        "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem"]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units = rows[0], rows[1]
+idx = {h: i for i, h in enumerate(hdr)}
+names = []
+for r in rows[2:]:
+    name = r[idx["Kernel Name"]]
+    names.append(name)
+    print("==", name[:110])
+    for w in WANT:
+        if w in idx:
+            print(f"   {w:68s} {r[idx[w]]:>16s} {units[idx[w]]}")
+for pat in sorted(set(n.split("(")[0].split("<")[0].split("::")[-1].split()[-1] for n in names)):
+    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + pat],
+                         capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(src)))
+    h = next((i for i, r in enumerate(rows) if r and r[0] == "Address"), None)
+    if h is None:
+        continue
+    hdr = rows[h]
+    si = hdr.index("Warp Stall Sampling (All Samples)")
+    stall_cols = [i for i, c in enumerate(hdr) if c.startswith("stall_") and "Not Issued" not in c]
+    data, tot_by = [], {hdr[i]: 0 for i in stall_cols}
+    seen = set()
+    for r in rows[h + 1:]:
+        if len(r) <= si or r[0] in seen or r[0] == "Address":
+            continue
+        seen.add(r[0])
+        try:
+            n = int(r[si])
+        except ValueError:
+            continue
+        data.append((n, r[1].strip(), r))
+        for i in stall_cols:
+            try:
+                tot_by[hdr[i]] += int(r[i])
+            except ValueError:
+                pass
+    tot = sum(d[0] for d in data) or 1
+    print(f"\n== stall samples, kernel ~{pat}: total {tot} (first launch)")
+    print("   by reason:", ", ".join(f"{k[6:]} {100 * v / tot:.1f}%" for k, v in sorted(tot_by.items(), key=lambda kv: -kv[1])[:8]))
+    for n, sass, r in sorted(data, key=lambda d: -d[0])[:14]:
+        print(f"   {100 * n / tot:5.1f}%  {sass[:100]}")
