@@ -58,6 +58,32 @@ void Homotopy<T>::contract(bool tc, int which, size_t rows, cudaStream_t st)
     counters[2] += rows;
 }
 
+template <typename T, int THREADS, int NCH, bool GS>
+static void launch_step_variant(unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
+{
+    static size_t configured = 0;   // per process; one device per process in every supported deployment
+    if (smem > 48 * 1024 && smem > configured) {
+        SSB_CUDA(cudaFuncSetAttribute(homotopy_step_kernel<T, THREADS, NCH, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = 200 * 1024;
+    }
+    homotopy_step_kernel<T, THREADS, NCH, GS><<<grid, THREADS, smem, st>>>(a, kb, ks);
+    SSB_CUDA(cudaGetLastError());
+}
+
+template <typename T>
+static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
+{
+#define SSB_STEP(TH, NC)                                                                          \
+    if (threads == TH && nch == NC) {                                                             \
+        if (gs) launch_step_variant<T, TH, NC, true>(grid, smem, st, a, kb, ks);                  \
+        else    launch_step_variant<T, TH, NC, false>(grid, smem, st, a, kb, ks);                 \
+        return;                                                                                   \
+    }
+    SSB_STEP(128, 1) SSB_STEP(128, 2) SSB_STEP(128, 4) SSB_STEP(256, 4) SSB_STEP(256, 0)
+#undef SSB_STEP
+    throw invalid_argument{ "no step-kernel variant for this shape" };
+}
+
 template <typename T>
 void Homotopy<T>::solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, int kmax, T* dX,
                               size_t ldx, uint32_t* d_iters, double* d_errs, cudaStream_t st)
@@ -93,11 +119,12 @@ void Homotopy<T>::solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint3
         counters[0]++;
     }
 
-    const size_t smem = homotopy_step_smem<T>(ws_kmax_, Npad);
-    SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
-    if (smem > 48 * 1024)
-        SSB_CUDA(cudaFuncSetAttribute(homotopy_step_kernel<T, STEP_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-
+    // step-kernel variant: c,q register-resident when the dictionary is narrow enough, inverse on chip when it fits
+    constexpr int V = 16 / sizeof(T);
+    const int chunks128 = (Npad + 128 * V - 1) / (128 * V), chunks256 = (Npad + 256 * V - 1) / (256 * V);
+    const int threads = chunks128 <= 4 ? 128 : 256;
+    const int nch = chunks128 <= 1 ? 1 : chunks128 <= 2 ? 2 : chunks128 <= 4 ? 4 : chunks256 <= 4 ? 4 : 0;
+    const size_t g_budget = 96 * 1024;
     size_t count = rows;
     int cur = 1;                 // P_[cur] holds the right-hand sides of this iteration
     int* d_counts = counts_.as<int>();
@@ -112,9 +139,13 @@ void Homotopy<T>::solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint3
         a.Pn = P_[cur ^ 1].template as<T>();
         a.Pn_lo = tc ? Plo_[cur ^ 1].template as<T>() : nullptr;
         a.it = it;
+        const int kb = (int)std::min<uint32_t>(it, (uint32_t)ws_kmax_);      // K <= kb before iteration `it`
+        const int ks = (kb + 1) | 1;                                          // odd row stride: conflict-free column reads
+        const bool gs = (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
+        const size_t smem = homotopy_step_smem<T>(ws_kmax_, Npad, gs ? kb + 1 : 0, ks);
+        SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
         const int span = begin_span(1, st);
-        homotopy_step_kernel<T, STEP_THREADS><<<(unsigned)count, STEP_THREADS, smem, st>>>(a);
-        SSB_CUDA(cudaGetLastError());
+        launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
         end_span(span, st);
         counters[0]++;
         counters[3]++;

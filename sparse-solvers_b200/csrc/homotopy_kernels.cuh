@@ -180,8 +180,15 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
 }
 
 // One homotopy iteration for one signal (homotopy-cpu.cpp:236-272).
-template <typename T, int THREADS>
-__global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
+//
+// Latency is what bounds this kernel (profiles/r1_ncu_step_and_contract_v1.txt: long-scoreboard + barrier stalls, DRAM
+// at 26 %), so everything that does not depend on the step size is fetched up front in ONE round trip -- c and q into
+// registers (NCH 16-byte chunks per thread), the active set, its direction and the K x K inverse into shared
+// memory -- and c / q are read from HBM exactly once per iteration.
+//   NCH  chunks of c,q a thread keeps in registers; 0 = dictionary too wide, c and q are re-read for the update
+//   GS   inverse held in shared memory (row stride ks) for the iteration; false = worked on in place in HBM
+template <typename T, int THREADS, int NCH, bool GS>
+__global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, int kb, int ks)
 {
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;
@@ -192,57 +199,93 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
     __shared__ uint32_t sh_idx;
     __shared__ int sh_slot, sh_row;
 
-    const int KC = a.Kmax + 1;
+    const int KC = (a.Kmax + 2) & ~1;   // even, keeps the arrays behind it 8-byte aligned
     T* s_d = reinterpret_cast<T*>(smem_raw);
     T* s_u1 = s_d + KC;
     T* s_u2 = s_u1 + KC;
     T* s_cg = s_u2 + KC;
-    uint32_t* s_gam = reinterpret_cast<uint32_t*>(s_cg + KC);
+    T* s_x = s_cg + KC;
+    uint32_t* s_gam = reinterpret_cast<uint32_t*>(s_x + KC);
     uint32_t* mask = s_gam + KC;
     const int mask_words = (a.ldc + 31) >> 5;
+    T* s_G = reinterpret_cast<T*>(mask + ((mask_words + 3) & ~3));
 
     const int pos = blockIdx.x;
     const int s = a.act ? a.act[pos] : pos;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    const int K = a.Kcur[s];
-    const T lam = a.lam[s];
     uint32_t* gam = a.gam + (size_t)s * a.Kmax;
     T* dG = a.dG + (size_t)s * a.Kmax;
     T* Ginv = a.Ginv + (size_t)s * a.Kmax * a.Kmax;
-    const int ldi = a.Kmax;
     T* c = a.C + (size_t)s * a.ldc;
     const T* q = a.Q + (size_t)pos * a.ldc;
     T* x = a.X + (size_t)s * a.ldx;
     const T TMAX = num_traits<T>::max();
+    T* Gm = GS ? s_G : Ginv;              // where the inverse is worked on
+    const int ldm = GS ? ks : a.Kmax;
 
+    // ---- one round trip: everything the iteration needs that does not depend on gamma
+    T cv[NCH > 0 ? NCH : 1][V], qv[NCH > 0 ? NCH : 1][V];
+    if constexpr (NCH > 0) {
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            const int i0 = (ch * THREADS + tid) * V;
+            if (i0 < a.ldc) {
+                *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(c + i0);
+                *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
+            }
+        }
+    }
+    const int K = a.Kcur[s];
+    const T lam = a.lam[s];
+    for (int k = tid; k < kb; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }   // K <= kb = min(it, Kmax)
+    if constexpr (GS) {
+        for (int e = tid; e < kb * kb; e += THREADS) {
+            const int r = e / kb, k = e - r * kb;
+            s_G[r * ks + k] = Ginv[(size_t)r * a.Kmax + k];
+        }
+    }
     for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
-    for (int k = tid; k < K; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }
     __syncthreads();
-    for (int k = tid; k < K; k += THREADS) atomicOr(&mask[s_gam[k] >> 5], 1u << (s_gam[k] & 31));
+    for (int k = tid; k < K; k += THREADS) {
+        const uint32_t g = s_gam[k];
+        atomicOr(&mask[g >> 5], 1u << (g & 31));
+        s_x[k] = x[g];
+    }
     __syncthreads();
 
     // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index
     T best = TMAX;
     uint32_t bidx = 0xffffffffu;
-    for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
-        T cv[V], qv[V];
-        *reinterpret_cast<int4*>(cv) = *reinterpret_cast<const int4*>(c + i0);
-        *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
+    auto scan = [&](const T (&cc)[V], const T (&qq)[V], int i0) {
         const uint32_t mw = mask[i0 >> 5] >> (i0 & 31);
 #pragma unroll
         for (int e = 0; e < V; ++e) {
             const int i = i0 + e;
             if (i < a.N && !((mw >> e) & 1u)) {
-                const T dl = T(1) - qv[e], dr = T(1) + qv[e];
-                if (dl != T(0)) { const T t = (lam - cv[e]) / dl; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
-                if (dr != T(0)) { const T t = (lam + cv[e]) / dr; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                const T dl = T(1) - qq[e], dr = T(1) + qq[e];
+                if (dl != T(0)) { const T t = (lam - cc[e]) / dl; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                if (dr != T(0)) { const T t = (lam + cc[e]) / dr; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
             }
+        }
+    };
+    if constexpr (NCH > 0) {
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            const int i0 = (ch * THREADS + tid) * V;
+            if (i0 < a.N) scan(cv[ch], qv[ch], i0);
+        }
+    } else {
+        for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
+            T cc[V], qq[V];
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
+            scan(cc, qq, i0);
         }
     }
     for (int k = tid; k < K; k += THREADS) {   // leave candidates, -x_i / d_i (:129-137)
         const uint32_t i = s_gam[k];
-        const T t = -x[i] / s_d[k];
+        const T t = -s_x[k] / s_d[k];
         if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
     }
     warp_argmin(best, bidx);
@@ -272,40 +315,58 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
         return;
     }
 
+    // ---- loads that depend on idx, issued before the streaming update so their latency is hidden
+    T dot = T(0);
+    if (!present) {
+        for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];   // u1 = A_G^T v (online_inverse.h:218)
+        dot = a.G[(size_t)idx * a.ldg + idx];                                                 // v.v
+    }
+
     // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
-    for (int k = tid; k < K; k += THREADS) x[s_gam[k]] += gamma * s_d[k];
+    for (int k = tid; k < K; k += THREADS) x[s_gam[k]] = s_x[k] + gamma * s_d[k];
 
     // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
     T mx = T(0);
-    for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
-        T cv[V], qv[V];
-        *reinterpret_cast<int4*>(cv) = *reinterpret_cast<const int4*>(c + i0);
-        *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
+    auto update = [&](T (&cc)[V], const T (&qq)[V], int i0) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            cv[e] = cv[e] - gamma * qv[e];
-            if (i0 + e < a.N) mx = max(mx, fabs(cv[e]));
+            cc[e] = cc[e] - gamma * qq[e];
+            if (i0 + e < a.N) mx = max(mx, fabs(cc[e]));
         }
-        *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(cv);
+        *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(cc);
+    };
+    if constexpr (NCH > 0) {
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            const int i0 = (ch * THREADS + tid) * V;
+            if (i0 < a.N) update(cv[ch], qv[ch], i0);
+        }
+    } else {
+        for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
+            T cc[V], qq[V];
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
+            update(cc, qq, i0);
+        }
     }
     mx = warp_max(mx);
     if (lane == 0) red_v[warp] = mx;
-    __syncthreads();   // also orders sh_slot and the c stores
+    __syncthreads();   // also orders sh_slot, s_u1 and the c stores
     if (tid == 0) {
         T m = red_v[0];
         for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
         sh_lam = m;
     }
+    // c at the (old-slot) active atoms and at a joining atom, for the signs; read back through L2 while the
+    // inverse is being updated
+    for (int k = tid; k < K + (present ? 0 : 1); k += THREADS) s_cg[k] = __ldcg(c + (k < K ? s_gam[k] : idx));
 
     // ---- toggle idx and update inv = (A_G^T A_G)^-1 (inverse_add_or_remove, :166-183)
     if (!present) {
         // online_inverse.h:203-249 (bordering); the new atom takes slot K
-        for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];   // u1 = A_G^T v
-        const T dot = a.G[(size_t)idx * a.ldg + idx];                                         // v.v
-        __syncthreads();
         for (int r = warp; r < K; r += NW) {                                                  // u2 = inv u1
             T acc = T(0);
-            for (int k = lane; k < K; k += 32) acc += Ginv[(size_t)r * ldi + k] * s_u1[k];
+            for (int k = lane; k < K; k += 32) acc += Gm[(size_t)r * ldm + k] * s_u1[k];
             acc = warp_sum(acc);
             if (lane == 0) s_u2[r] = acc;
         }
@@ -316,48 +377,54 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
         const T dd = T(1) / (dot - uu);                                                       // :228
         for (int e = tid; e < K * K; e += THREADS) {                                          // inv += d u2 u2^T
             const int r = e / K, k = e - r * K;
-            Ginv[(size_t)r * ldi + k] += (dd * s_u2[r]) * s_u2[k];
+            Gm[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
         }
         for (int r = tid; r < K; r += THREADS) {                                              // border -d u2, corner d
             const T u3 = -dd * s_u2[r];
-            Ginv[(size_t)r * ldi + K] = u3;
-            Ginv[(size_t)K * ldi + r] = u3;
+            Gm[(size_t)r * ldm + K] = u3;
+            Gm[(size_t)K * ldm + r] = u3;
         }
-        if (tid == 0) { Ginv[(size_t)K * ldi + K] = dd; s_gam[K] = idx; gam[K] = idx; }
+        if (tid == 0) { Gm[(size_t)K * ldm + K] = dd; s_gam[K] = idx; gam[K] = idx; }
     } else {
         // online_inverse.h:253-293; the leaving atom sits in slot j
         const int j = sh_slot;
-        const T dd = Ginv[(size_t)j * ldi + j];
+        const T dd = Gm[(size_t)j * ldm + j];
         const T sc = -(T(1) / dd);
-        for (int r = tid; r < K; r += THREADS) s_u1[r] = Ginv[(size_t)r * ldi + j] * sc;       // u = -col/d
+        for (int r = tid; r < K; r += THREADS) s_u1[r] = Gm[(size_t)r * ldm + j] * sc;         // u = -col/d
         __syncthreads();
         for (int e = tid; e < K * K; e += THREADS) {                                          // inv -= d u u^T
             const int r = e / K, k = e - r * K;
-            if (r != j && k != j) Ginv[(size_t)r * ldi + k] += (-dd * s_u1[r]) * s_u1[k];
+            if (r != j && k != j) Gm[(size_t)r * ldm + k] += (-dd * s_u1[r]) * s_u1[k];
         }
         __syncthreads();
         const int last = K - 1;
         if (j != last) {   // refill slot j with the last slot (reads touch row/col `last` only, writes never do)
             for (int k = tid; k < last; k += THREADS) {
                 const int kk = (k == j) ? last : k;
-                const T vrow = Ginv[(size_t)last * ldi + kk];
-                const T vcol = Ginv[(size_t)kk * ldi + last];
-                Ginv[(size_t)j * ldi + k] = vrow;
-                Ginv[(size_t)k * ldi + j] = vcol;
+                const T vrow = Gm[(size_t)last * ldm + kk];
+                const T vcol = Gm[(size_t)kk * ldm + last];
+                Gm[(size_t)j * ldm + k] = vrow;
+                Gm[(size_t)k * ldm + j] = vcol;
             }
-            if (tid == 0) { const uint32_t g = s_gam[last]; s_gam[j] = g; gam[j] = g; }
+            if (tid == 0) { const uint32_t g = s_gam[last]; s_gam[j] = g; gam[j] = g; s_cg[j] = s_cg[last]; }
         }
     }
     __syncthreads();
 
     // ---- d_G = inv * sign(c_G, tol) (:259-263); the tolerance is also the sign dead-band
-    for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(c[s_gam[k]], a.tol);
+    for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(s_cg[k], a.tol);
     __syncthreads();
     for (int r = warp; r < Knew; r += NW) {
         T acc = T(0);
-        for (int k = lane; k < Knew; k += 32) acc += Ginv[(size_t)r * ldi + k] * s_cg[k];
+        for (int k = lane; k < Knew; k += 32) acc += Gm[(size_t)r * ldm + k] * s_cg[k];
         acc = warp_sum(acc);
         if (lane == 0) { s_d[r] = acc; dG[r] = acc; }
+    }
+    if constexpr (GS) {   // the updated inverse goes back to HBM for the next iteration
+        for (int e = tid; e < Knew * Knew; e += THREADS) {
+            const int r = e / Knew, k = e - r * Knew;
+            Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
+        }
     }
     const T lam_new = sh_lam;
     const bool cont = (a.it < a.max_iter) && (lam_new > a.tol);   // :272
@@ -377,9 +444,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a)
     if (cont) write_rhs<T, THREADS>(a, sh_row, s_gam, s_d, Knew);
 }
 
+// dynamic shared memory of the step kernel: per-slot vectors, membership mask, and (when held on chip) the inverse
 template <typename T>
-inline size_t homotopy_step_smem(int Kmax, int ldc) {
-    return (size_t)(Kmax + 1) * (4 * sizeof(T) + sizeof(uint32_t)) + (size_t)((ldc + 31) / 32) * sizeof(uint32_t);
+inline size_t homotopy_step_smem(int Kmax, int ldc, int g_rows, int ks) {
+    const size_t mask_words = (size_t)((ldc + 31) / 32 + 3) & ~(size_t)3;
+    return (size_t)((Kmax + 2) & ~1) * (5 * sizeof(T) + sizeof(uint32_t)) + mask_words * sizeof(uint32_t) + (size_t)g_rows * ks * sizeof(T) + 16;
 }
 
 }  // namespace ssb
