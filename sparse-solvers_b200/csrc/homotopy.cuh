@@ -5,6 +5,11 @@
 #pragma once
 
 #include <algorithm>
+#include <atomic>
+#include <exception>
+#include <memory>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 #include "contract_simt.cuh"
@@ -57,10 +62,11 @@ template <typename T>
 class Homotopy : public SolverBase {
 public:
     static constexpr int STEP_THREADS = 128;
+    static constexpr int MAX_LANES = 2;
 
     Homotopy(int dev)
         : SolverBase(sizeof(T) == 4 ? SolverKind::HomotopyF32 : SolverKind::HomotopyF64, dev) {}
-    ~Homotopy() override { if (plan_[0]) tc_plan_destroy(plan_[0]); if (plan_[1]) tc_plan_destroy(plan_[1]); if (plan_y_) tc_plan_destroy(plan_y_); }
+    ~Homotopy() override { lanes_.clear(); }
 
     int M = 0, N = 0, Mp = 0, Npad = 0;
 
@@ -72,23 +78,23 @@ public:
         for (size_t j = 0; j < n; ++j)
             for (size_t i = 0; i < m; ++i)
                 packed[j * Mp + i] = A[(ptrdiff_t)i * rs + (ptrdiff_t)j * cs];
-        At_.reserve(packed.size() * sizeof(T));
-        SSB_CUDA(cudaMemcpyAsync(At_.p, packed.data(), packed.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
+        alloc_dictionary();
+        SSB_CUDA(cudaMemcpyAsync(At_, packed.data(), packed.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
         SSB_CUDA(cudaStreamSynchronize(stream));
         finish_dictionary();
     }
     // A already on this device
     void set_dictionary_dev(const T* dA, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs) {
         check_shape(m, n);
-        At_.reserve((size_t)Npad * Mp * sizeof(T));
-        pack_dictionary_kernel<T><<<1024, 256, 0, stream>>>(dA, (long long)rs, (long long)cs, M, N, At_.as<T>(), Mp, Npad);
+        alloc_dictionary();
+        pack_dictionary_kernel<T><<<1024, 256, 0, stream>>>(dA, (long long)rs, (long long)cs, M, N, At_, Mp, Npad);
         SSB_CUDA(cudaGetLastError());
         counters[0]++;
         finish_dictionary();
     }
 
     void solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
-                         uint32_t* d_iters, double* d_errs, cudaStream_t st);
+                         uint32_t* d_iters, double* d_errs, cudaStream_t user_stream);
     void solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* X, size_t ldx,
                           uint32_t* iters, double* errs);
     void reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, size_t ldy);
@@ -97,15 +103,50 @@ public:
     double debug_contract(const T* P, size_t rows, T* Q, int path, int reps);
 
 private:
-    dev_buffer At_, At_hi_, At_lo_, G_;
-    // per-chunk workspace
-    dev_buffer C_, Q_, P_[2], Plo_[2], gam_, dG_, Ginv_, lam_, K_, act_[2], counts_;
-    dev_buffer stY_, stX_, stIt_, stErr_;   // staging for the host-pointer entry points
-    pinned_buffer h_count_;
-    TcPlan* plan_[2] = { nullptr, nullptr };
-    TcPlan* plan_y_ = nullptr;
-    size_t ws_rows_ = 0;   // rows the workspace was sized for
-    int ws_kmax_ = 0;
+    // One lane = one sub-batch in flight: its own stream and workspace.  Two lanes run concurrently so that one
+    // lane's tensor-bound contraction overlaps the other's HBM/latency-bound step kernel (and, on the host-pointer
+    // path, its H2D / D2H copies).
+    struct Lane {
+        cudaStream_t stream = nullptr;
+        dev_buffer C, Q, P[2], Plo[2], gam, dG, Ginv, lam, K, act[2], counts;
+        dev_buffer stY, stX, stIt, stErr;     // staging for the host-pointer entry points
+        pinned_buffer h_count;
+        TcPlan* plan[2] = { nullptr, nullptr };
+        size_t ws_rows = 0;
+        int ws_kmax = 0;
+        // instrumentation, merged into the handle after the solve
+        uint64_t counters[4] = { 0, 0, 0, 0 };
+        struct span { cudaEvent_t a, b; int cls; };
+        std::vector<span> spans;
+        std::vector<cudaEvent_t> pool;
+        Lane() { SSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
+        ~Lane() {
+            drop_plans();
+            for (auto e : pool) cudaEventDestroy(e);
+            for (auto& s : spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+            if (stream) cudaStreamDestroy(stream);
+        }
+        void drop_plans() { for (auto& p : plan) { if (p) tc_plan_destroy(p); p = nullptr; } }
+        cudaEvent_t event() {
+            if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+            cudaEvent_t e; SSB_CUDA(cudaEventCreate(&e)); return e;
+        }
+        int begin(bool on, int cls) {
+            if (!on) return -1;
+            span s{ event(), event(), cls };
+            SSB_CUDA(cudaEventRecord(s.a, stream));
+            spans.push_back(s);
+            return (int)spans.size() - 1;
+        }
+        void end(int id) { if (id >= 0) SSB_CUDA(cudaEventRecord(spans[id].b, stream)); }
+        size_t ws_bytes() const { return C.bytes + Q.bytes + P[0].bytes + P[1].bytes + Plo[0].bytes + Plo[1].bytes + Ginv.bytes; }
+    };
+
+    dev_buffer dict_;                 // At | At_hi | At_lo | G in one slab (one L2 persistence window covers it)
+    T* At_ = nullptr; T* At_hi_ = nullptr; T* At_lo_ = nullptr; T* G_ = nullptr;
+    std::vector<std::unique_ptr<Lane>> lanes_;
+    std::mutex merge_mu_;
+    size_t l2_set_aside_ = 0;
 
     void check_shape(size_t m, size_t n) {
         SSB_REQUIRE(m > 0 && n > 0, "dictionary must be non-empty");
@@ -115,42 +156,28 @@ private:
         Mp = (int)round_up(m, 32);
         Npad = (int)round_up(n, 128);
     }
-
-    void finish_dictionary() {
-        // Gram matrix G = A^T A, [N][Npad]: the contraction with P := At
-        G_.reserve((size_t)Npad * Npad * sizeof(T));
-        counters[0] += launch_contract_simt<T>(At_.as<T>(), Mp, Npad, Mp, At_.as<T>(), Mp, Npad, G_.as<T>(), Npad, stream);
-        if constexpr (sizeof(T) == 4) {
-            At_hi_.reserve((size_t)Npad * Mp * sizeof(T));
-            At_lo_.reserve((size_t)Npad * Mp * sizeof(T));
-            tf32_split_kernel<<<1024, 256, 0, stream>>>(At_.as<float>(), At_hi_.as<float>(), At_lo_.as<float>(), (size_t)Npad * Mp);
-            SSB_CUDA(cudaGetLastError());
-            counters[0]++;
-        }
-        SSB_CUDA(cudaStreamSynchronize(stream));
-        drop_plans();
+    void alloc_dictionary() {
+        const size_t a = (size_t)Npad * Mp, g = (size_t)Npad * Npad;
+        const size_t parts = sizeof(T) == 4 ? 3 : 1;
+        dict_.reserve((parts * a + g) * sizeof(T));
+        At_ = dict_.as<T>();
+        At_hi_ = sizeof(T) == 4 ? At_ + a : nullptr;
+        At_lo_ = sizeof(T) == 4 ? At_ + 2 * a : nullptr;
+        G_ = At_ + parts * a;
     }
-    void drop_plans() {
-        for (auto& p : plan_) { if (p) tc_plan_destroy(p); p = nullptr; }
-        if (plan_y_) { tc_plan_destroy(plan_y_); plan_y_ = nullptr; }
+    void finish_dictionary();
+    Lane& lane(int i) {
+        while ((int)lanes_.size() <= i) lanes_.emplace_back(new Lane());
+        return *lanes_[i];
     }
+    void apply_l2_policy(cudaStream_t st);
 
     size_t bytes_per_signal(int kmax) const {
         return (size_t)(2 * Npad + 4 * Mp + (size_t)kmax * kmax + 2 * kmax + 4) * sizeof(T) + 6 * sizeof(int);
     }
-    size_t choose_chunk(size_t batch, int kmax) const {
-        size_t free_b = 0, total_b = 0;
-        SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        const size_t budget = std::min<size_t>((size_t)(0.6 * (double)free_b) + ws_bytes(), (size_t)24 << 30);
-        size_t chunk = std::max<size_t>(1, budget / bytes_per_signal(kmax));
-        chunk = std::min<size_t>(chunk, 65536);
-        if (chunk >= 256) chunk = chunk / 256 * 256;
-        return std::min(chunk, batch);
-    }
-    size_t ws_bytes() const {
-        return C_.bytes + Q_.bytes + P_[0].bytes + P_[1].bytes + Plo_[0].bytes + Plo_[1].bytes + Ginv_.bytes;
-    }
-    void reserve_workspace(size_t rows, int kmax);
+    // signals per chunk and number of lanes for a batch
+    void plan_batch(size_t batch, int kmax, size_t& chunk, int& nlanes);
+    void reserve_workspace(Lane& L, size_t rows, int kmax);
     bool use_tc(size_t rows) const {
         if (sizeof(T) != 4) return false;
         if (contraction_path == 1) return false;
@@ -158,9 +185,11 @@ private:
         if (contraction_path == 2) return true;
         return rows >= 64;   // below that the tiles are mostly padding and the SIMT kernels win
     }
-    void contract(bool tc, int which, size_t rows, cudaStream_t st);
-    void solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, int kmax, T* dX, size_t ldx,
-                     uint32_t* d_iters, double* d_errs, cudaStream_t st);
+    void contract(Lane& L, bool tc, int which, size_t rows);
+    void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
+                     uint32_t* d_iters, double* d_errs);
+    void merge(Lane& L);
+    template <typename F> void run_lanes(int nlanes, size_t nchunks, F&& body);
 };
 
 }  // namespace ssb

@@ -1,62 +1,127 @@
 // Member definitions of ssb::Homotopy<T> (included by homotopy.cuh).
 #pragma once
 
+#include <cstdlib>
+
 namespace ssb {
 
 template <typename T>
-void Homotopy<T>::reserve_workspace(size_t rows, int kmax)
+void Homotopy<T>::finish_dictionary()
 {
-    const size_t rows_alloc = round_up(rows, 256);
-    if (rows_alloc <= ws_rows_ && kmax <= ws_kmax_) return;
-    const size_t r = std::max(rows_alloc, ws_rows_);
-    const int k = std::max(kmax, ws_kmax_);
-    drop_plans();
-    C_.reserve(r * Npad * sizeof(T));
-    Q_.reserve(r * Npad * sizeof(T));
-    for (int i = 0; i < 2; ++i) {
-        const bool grew = P_[i].bytes < r * Mp * sizeof(T);
-        P_[i].reserve(r * Mp * sizeof(T));
-        if (grew) SSB_CUDA(cudaMemsetAsync(P_[i].p, 0, P_[i].bytes, stream));   // rows past `count` feed the tensor tiles
-        if (sizeof(T) == 4) {
-            const bool grew_lo = Plo_[i].bytes < r * Mp * sizeof(T);
-            Plo_[i].reserve(r * Mp * sizeof(T));
-            if (grew_lo) SSB_CUDA(cudaMemsetAsync(Plo_[i].p, 0, Plo_[i].bytes, stream));
-        }
-        act_[i].reserve(r * sizeof(int));
+    // Gram matrix G = A^T A, [Npad][Npad]: the contraction with P := At
+    counters[0] += launch_contract_simt<T>(At_, Mp, Npad, Mp, At_, Mp, Npad, G_, Npad, stream);
+    if constexpr (sizeof(T) == 4) {
+        tf32_split_kernel<<<1024, 256, 0, stream>>>(At_, At_hi_, At_lo_, (size_t)Npad * Mp);
+        SSB_CUDA(cudaGetLastError());
+        counters[0]++;
     }
-    gam_.reserve(r * k * sizeof(uint32_t));
-    dG_.reserve(r * k * sizeof(T));
-    Ginv_.reserve(r * (size_t)k * k * sizeof(T));
-    lam_.reserve(r * sizeof(T));
-    K_.reserve(r * sizeof(int));
-    counts_.reserve(2 * sizeof(int));
-    h_count_.reserve(sizeof(int));
     SSB_CUDA(cudaStreamSynchronize(stream));
-    ws_rows_ = r;
-    ws_kmax_ = k;
+    for (auto& l : lanes_) l->drop_plans();
 }
 
-// Q[r][:] = A^T P_[which][r][:] for r < rows
+// marks the dictionary slab as persisting in L2 for work on `st` (c, q, P, Ginv traffic is streaming)
 template <typename T>
-void Homotopy<T>::contract(bool tc, int which, size_t rows, cudaStream_t st)
+void Homotopy<T>::apply_l2_policy(cudaStream_t st)
 {
-    const int span = begin_span(0, st);
+    int max_window = 0, max_persist = 0;
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device);
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device);
+    if (max_window <= 0 || max_persist <= 0 || !dict_.p) { cudaGetLastError(); return; }
+    if (const char* e = getenv("SSB200_L2_PERSIST")) if (atoi(e) == 0) return;                        // tuning knob
+    // set aside only what the dictionary slab needs: the rest of L2 keeps serving the streaming state
+    const size_t want = std::min<size_t>(round_up(dict_.bytes, (size_t)1 << 20), (size_t)max_persist);
+    if (l2_set_aside_ != want) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want); l2_set_aside_ = want; }
+    cudaStreamAttrValue v{};
+    const size_t win = std::min<size_t>(dict_.bytes, (size_t)max_window);
+    v.accessPolicyWindow.base_ptr = dict_.p;
+    v.accessPolicyWindow.num_bytes = win;
+    v.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)win);
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
+    cudaGetLastError();
+}
+
+template <typename T>
+void Homotopy<T>::plan_batch(size_t batch, int kmax, size_t& chunk, int& nlanes)
+{
+    size_t free_b = 0, total_b = 0;
+    SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    size_t held = 0;
+    for (auto& l : lanes_) held += l->ws_bytes();
+    const size_t budget = std::min<size_t>((size_t)(0.6 * (double)free_b) + held, (size_t)32 << 30);
+    nlanes = 1;   // measured (profiles/r1_lanes_experiment.txt): one lane with the largest chunk wins at C2
+    if (const char* e = getenv("SSB200_LANES")) nlanes = std::max(1, std::min(MAX_LANES, atoi(e)));   // tuning knob
+    size_t cap = std::max<size_t>(1, budget / nlanes / bytes_per_signal(kmax));
+    size_t cap_max = 65536;
+    if (const char* e = getenv("SSB200_CHUNK")) cap_max = std::max(256, atoi(e));                     // tuning knob
+    cap = std::min<size_t>(cap, cap_max);
+    if (cap >= 256) cap = cap / 256 * 256;
+    // even split over the lanes, in multiples of 256 signals
+    size_t per = (batch + nlanes - 1) / nlanes;
+    if (per > 256) per = round_up(per, 256);
+    const size_t pieces = (per + cap - 1) / cap;
+    chunk = (per + pieces - 1) / pieces;
+    if (chunk > 256) chunk = round_up(chunk, 256);
+    chunk = std::min(std::min(chunk, cap), batch);
+}
+
+template <typename T>
+void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
+{
+    const size_t rows_alloc = round_up(rows, 256);
+    if (rows_alloc <= L.ws_rows && kmax <= L.ws_kmax) return;
+    const size_t r = std::max(rows_alloc, L.ws_rows);
+    const int k = std::max(kmax, L.ws_kmax);
+    L.drop_plans();
+    L.C.reserve(r * Npad * sizeof(T));
+    L.Q.reserve(r * Npad * sizeof(T));
+    for (int i = 0; i < 2; ++i) {
+        const bool grew = L.P[i].bytes < r * Mp * sizeof(T);
+        L.P[i].reserve(r * Mp * sizeof(T));
+        if (grew) SSB_CUDA(cudaMemsetAsync(L.P[i].p, 0, L.P[i].bytes, L.stream));   // rows past `count` feed the tensor tiles
+        if (sizeof(T) == 4) {
+            const bool grew_lo = L.Plo[i].bytes < r * Mp * sizeof(T);
+            L.Plo[i].reserve(r * Mp * sizeof(T));
+            if (grew_lo) SSB_CUDA(cudaMemsetAsync(L.Plo[i].p, 0, L.Plo[i].bytes, L.stream));
+        }
+        L.act[i].reserve(r * sizeof(int));
+    }
+    L.gam.reserve(r * k * sizeof(uint32_t));
+    L.dG.reserve(r * k * sizeof(T));
+    L.Ginv.reserve(r * (size_t)k * k * sizeof(T));
+    L.lam.reserve(r * sizeof(T));
+    L.K.reserve(r * sizeof(int));
+    L.counts.reserve(2 * sizeof(int));
+    L.h_count.reserve(sizeof(int));
+    SSB_CUDA(cudaStreamSynchronize(L.stream));
+    L.ws_rows = r;
+    L.ws_kmax = k;
+    apply_l2_policy(L.stream);
+}
+
+// Q[r][:] = A^T P[which][r][:] for r < rows
+template <typename T>
+void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows)
+{
+    const int span = L.begin(timing, 0);
     if constexpr (sizeof(T) == 4) {
         if (tc) {
-            if (!plan_[which])
-                plan_[which] = tc_plan_create(At_hi_.as<float>(), At_lo_.as<float>(), Npad, Mp,
-                                              P_[which].template as<float>(), Plo_[which].template as<float>(), (int)ws_rows_);
-            tc_contract(plan_[which], (int)rows, Q_.as<float>(), Npad, st);
-            counters[0]++;
+            if (!L.plan[which])
+                L.plan[which] = tc_plan_create(At_hi_, At_lo_, Npad, Mp, L.P[which].template as<float>(),
+                                               L.Plo[which].template as<float>(), (int)L.ws_rows);
+            tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream);
+            L.counters[0]++;
         }
     }
     if (!tc)
-        counters[0] += launch_contract_simt<T>(At_.as<T>(), Mp, Npad, Mp, P_[which].template as<T>(), Mp, (int)rows,
-                                               Q_.as<T>(), Npad, st);
-    end_span(span, st);
-    counters[1]++;
-    counters[2] += rows;
+        L.counters[0] += launch_contract_simt<T>(At_, Mp, Npad, Mp, L.P[which].template as<T>(), Mp, (int)rows,
+                                                 L.Q.template as<T>(), Npad, L.stream);
+    L.end(span);
+    L.counters[1]++;
+    L.counters[2] += rows;
 }
+
 
 template <typename T, int THREADS, int NCH, bool GS>
 static void launch_step_variant(unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
@@ -84,39 +149,41 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
     throw invalid_argument{ "no step-kernel variant for this shape" };
 }
 
+
 template <typename T>
-void Homotopy<T>::solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, int kmax, T* dX,
-                              size_t ldx, uint32_t* d_iters, double* d_errs, cudaStream_t st)
+void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX,
+                              size_t ldx, uint32_t* d_iters, double* d_errs)
 {
+    cudaStream_t st = L.stream;
     const bool tc = use_tc(rows);
     HomArgs<T> a{};
-    a.N = N; a.ldc = Npad; a.Mp = Mp; a.ldp = Mp; a.Kmax = ws_kmax_;
-    a.At = At_.as<T>(); a.G = G_.as<T>(); a.ldg = Npad;
-    a.C = C_.as<T>(); a.Q = Q_.as<T>(); a.X = dX; a.ldx = ldx;
-    a.gam = gam_.as<uint32_t>(); a.dG = dG_.as<T>(); a.Ginv = Ginv_.as<T>(); a.lam = lam_.as<T>(); a.Kcur = K_.as<int>();
+    a.N = N; a.ldc = Npad; a.Mp = Mp; a.ldp = Mp; a.Kmax = L.ws_kmax;
+    a.At = At_; a.G = G_; a.ldg = Npad;
+    a.C = L.C.template as<T>(); a.Q = L.Q.template as<T>(); a.X = dX; a.ldx = ldx;
+    a.gam = L.gam.template as<uint32_t>(); a.dG = L.dG.template as<T>(); a.Ginv = L.Ginv.template as<T>();
+    a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>();
     a.iters = d_iters; a.errs = d_errs;
     a.split = tc ? 1 : 0;
     a.tol = tol; a.max_iter = max_iter;
-    (void)kmax;
 
     // c0 = A^T y for the whole chunk (homotopy-cpu.cpp:215)
     {
         const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
-        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, P_[0].template as<T>(),
-                                                       tc ? Plo_[0].template as<T>() : nullptr, Mp, a.split);
+        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, L.P[0].template as<T>(),
+                                                       tc ? L.Plo[0].template as<T>() : nullptr, Mp, a.split);
         SSB_CUDA(cudaGetLastError());
-        counters[0]++;
+        L.counters[0]++;
     }
-    contract(tc, 0, rows, st);
+    contract(L, tc, 0, rows);
     {
         a.act = nullptr; a.act_next = nullptr; a.next_count = nullptr;
-        a.Pn = P_[1].template as<T>(); a.Pn_lo = tc ? Plo_[1].template as<T>() : nullptr;
+        a.Pn = L.P[1].template as<T>(); a.Pn_lo = tc ? L.Plo[1].template as<T>() : nullptr;
         a.it = 0;
-        const int span = begin_span(1, st);
+        const int span = L.begin(timing, 1);
         homotopy_init_kernel<T, STEP_THREADS><<<(unsigned)rows, STEP_THREADS, 0, st>>>(a);
         SSB_CUDA(cudaGetLastError());
-        end_span(span, st);
-        counters[0]++;
+        L.end(span);
+        L.counters[0]++;
     }
 
     // step-kernel variant: c,q register-resident when the dictionary is narrow enough, inverse on chip when it fits
@@ -125,55 +192,104 @@ void Homotopy<T>::solve_chunk(const T* dY, size_t rows, size_t ldy, T tol, uint3
     const int threads = chunks128 <= 4 ? 128 : 256;
     const int nch = chunks128 <= 1 ? 1 : chunks128 <= 2 ? 2 : chunks128 <= 4 ? 4 : chunks256 <= 4 ? 4 : 0;
     const size_t g_budget = 96 * 1024;
+
     size_t count = rows;
-    int cur = 1;                 // P_[cur] holds the right-hand sides of this iteration
-    int* d_counts = counts_.as<int>();
-    int* h_count = h_count_.as<int>();
+    int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
+    int* d_counts = L.counts.template as<int>();
+    int* h_count = L.h_count.template as<int>();
     for (uint32_t it = 1; it <= max_iter && count > 0; ++it) {
-        contract(tc, cur, count, st);
+        contract(L, tc, cur, count);
         int* next_count = d_counts + (it & 1);
         SSB_CUDA(cudaMemsetAsync(next_count, 0, sizeof(int), st));
-        a.act = (it == 1) ? nullptr : act_[cur].template as<int>();
-        a.act_next = act_[cur ^ 1].template as<int>();
+        a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
+        a.act_next = L.act[cur ^ 1].template as<int>();
         a.next_count = next_count;
-        a.Pn = P_[cur ^ 1].template as<T>();
-        a.Pn_lo = tc ? Plo_[cur ^ 1].template as<T>() : nullptr;
+        a.Pn = L.P[cur ^ 1].template as<T>();
+        a.Pn_lo = tc ? L.Plo[cur ^ 1].template as<T>() : nullptr;
         a.it = it;
-        const int kb = (int)std::min<uint32_t>(it, (uint32_t)ws_kmax_);      // K <= kb before iteration `it`
+        const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
         const int ks = (kb + 1) | 1;                                          // odd row stride: conflict-free column reads
         const bool gs = (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
-        const size_t smem = homotopy_step_smem<T>(ws_kmax_, Npad, gs ? kb + 1 : 0, ks);
+        const size_t smem = homotopy_step_smem<T>(L.ws_kmax, Npad, gs ? kb + 1 : 0, ks);
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
-        const int span = begin_span(1, st);
+        const int span = L.begin(timing, 1);
         launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
-        end_span(span, st);
-        counters[0]++;
-        counters[3]++;
+        L.end(span);
+        L.counters[0]++;
+        L.counters[3]++;
         SSB_CUDA(cudaMemcpyAsync(h_count, next_count, sizeof(int), cudaMemcpyDeviceToHost, st));
         SSB_CUDA(cudaStreamSynchronize(st));
         count = (size_t)*h_count;
         cur ^= 1;
     }
     SSB_CUDA(cudaStreamSynchronize(st));
-    collect_spans();
+}
+
+// folds a lane's counters and event-timed spans into the handle (stream already synchronised)
+template <typename T>
+void Homotopy<T>::merge(Lane& L)
+{
+    std::lock_guard<std::mutex> g(merge_mu_);
+    for (int i = 0; i < 4; ++i) { counters[i] += L.counters[i]; L.counters[i] = 0; }
+    for (auto& s : L.spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) ms[s.cls] += t;
+        L.pool.push_back(s.a);
+        L.pool.push_back(s.b);
+    }
+    L.spans.clear();
+}
+
+// runs body(lane, chunk_index) over nchunks chunks on nlanes lanes; lane 0 is the calling thread
+template <typename T>
+template <typename F>
+void Homotopy<T>::run_lanes(int nlanes, size_t nchunks, F&& body)
+{
+    std::atomic<size_t> next{ 0 };
+    std::exception_ptr err[MAX_LANES] = {};
+    auto worker = [&](int li) {
+        try {
+            SSB_CUDA(cudaSetDevice(device));
+            Lane& L = lane(li);
+            for (;;) {
+                const size_t c = next.fetch_add(1);
+                if (c >= nchunks) break;
+                body(L, c);
+            }
+            merge(L);
+        } catch (...) {
+            err[li] = std::current_exception();
+            next.store(nchunks);     // stop the other lane from taking new chunks
+        }
+    };
+    for (int li = 0; li < nlanes; ++li) lane(li);          // create lanes on the calling thread
+    std::vector<std::thread> helpers;
+    for (int li = 1; li < nlanes; ++li) helpers.emplace_back(worker, li);
+    worker(0);
+    for (auto& t : helpers) t.join();
+    for (int li = 0; li < nlanes; ++li) if (err[li]) std::rethrow_exception(err[li]);
 }
 
 template <typename T>
 void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
-                                  uint32_t* d_iters, double* d_errs, cudaStream_t st)
+                                  uint32_t* d_iters, double* d_errs, cudaStream_t user_stream)
 {
     SSB_REQUIRE(M > 0, "no dictionary");
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");   // homotopy-cpu.cpp:199
     if (batch == 0) return;
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
-    if (!st) st = stream;
+    // inputs produced on the caller's stream must be complete before the lanes read them
+    SSB_CUDA(cudaStreamSynchronize(user_stream));
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
-    const size_t chunk = choose_chunk(batch, kmax);
-    reserve_workspace(chunk, kmax);
-    for (size_t b0 = 0; b0 < batch; b0 += chunk) {
-        const size_t rows = std::min(chunk, batch - b0);
-        solve_chunk(dY + b0 * ldy, rows, ldy, tol, max_iter, kmax, dX + b0 * ldx, ldx, d_iters + b0, d_errs + b0, st);
-    }
+    size_t chunk; int nlanes;
+    plan_batch(batch, kmax, chunk, nlanes);
+    const size_t nchunks = (batch + chunk - 1) / chunk;
+    nlanes = (int)std::min<size_t>(nlanes, nchunks);
+    for (int li = 0; li < nlanes; ++li) reserve_workspace(lane(li), chunk, kmax);
+    run_lanes(nlanes, nchunks, [&](Lane& L, size_t c) {
+        const size_t b0 = c * chunk, rows = std::min(chunk, batch - b0);
+        solve_chunk(L, dY + b0 * ldy, rows, ldy, tol, max_iter, dX + b0 * ldx, ldx, d_iters + b0, d_errs + b0);
+    });
 }
 
 template <typename T>
@@ -185,52 +301,61 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     if (batch == 0) return;
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
-    const size_t chunk = choose_chunk(batch, kmax);
-    reserve_workspace(chunk, kmax);
-    stY_.reserve(chunk * M * sizeof(T));
-    stX_.reserve(chunk * N * sizeof(T));
-    stIt_.reserve(chunk * sizeof(uint32_t));
-    stErr_.reserve(chunk * sizeof(double));
-    for (size_t b0 = 0; b0 < batch; b0 += chunk) {
-        const size_t rows = std::min(chunk, batch - b0);
-        SSB_CUDA(cudaMemcpy2DAsync(stY_.p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
-                                   cudaMemcpyHostToDevice, stream));
-        solve_chunk(stY_.as<T>(), rows, M, tol, max_iter, kmax, stX_.as<T>(), N, stIt_.as<uint32_t>(),
-                    stErr_.as<double>(), stream);
-        SSB_CUDA(cudaMemcpy2DAsync(X + b0 * ldx, ldx * sizeof(T), stX_.p, N * sizeof(T), N * sizeof(T), rows,
-                                   cudaMemcpyDeviceToHost, stream));
-        SSB_CUDA(cudaMemcpyAsync(iters + b0, stIt_.p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-        SSB_CUDA(cudaMemcpyAsync(errs + b0, stErr_.p, rows * sizeof(double), cudaMemcpyDeviceToHost, stream));
-        SSB_CUDA(cudaStreamSynchronize(stream));
+    size_t chunk; int nlanes;
+    plan_batch(batch, kmax, chunk, nlanes);
+    // smaller pieces on the host path: one lane's copies overlap the other lane's kernels
+    if (batch >= 8192) chunk = std::min<size_t>(chunk, std::max<size_t>(2048, round_up(batch / 8, 256)));
+    const size_t nchunks = (batch + chunk - 1) / chunk;
+    nlanes = (int)std::min<size_t>(nlanes, nchunks);
+    for (int li = 0; li < nlanes; ++li) {
+        Lane& L = lane(li);
+        reserve_workspace(L, chunk, kmax);
+        L.stY.reserve(chunk * M * sizeof(T));
+        L.stX.reserve(chunk * N * sizeof(T));
+        L.stIt.reserve(chunk * sizeof(uint32_t));
+        L.stErr.reserve(chunk * sizeof(double));
     }
+    run_lanes(nlanes, nchunks, [&](Lane& L, size_t c) {
+        const size_t b0 = c * chunk, rows = std::min(chunk, batch - b0);
+        SSB_CUDA(cudaMemcpy2DAsync(L.stY.p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
+                                   cudaMemcpyHostToDevice, L.stream));
+        solve_chunk(L, L.stY.template as<T>(), rows, M, tol, max_iter, L.stX.template as<T>(), N,
+                    L.stIt.template as<uint32_t>(), L.stErr.template as<double>());
+        SSB_CUDA(cudaMemcpy2DAsync(X + b0 * ldx, ldx * sizeof(T), L.stX.p, N * sizeof(T), N * sizeof(T), rows,
+                                   cudaMemcpyDeviceToHost, L.stream));
+        SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt.p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream));
+        SSB_CUDA(cudaMemcpyAsync(errs + b0, L.stErr.p, rows * sizeof(double), cudaMemcpyDeviceToHost, L.stream));
+        SSB_CUDA(cudaStreamSynchronize(L.stream));
+    });
 }
 
 template <typename T>
 double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int reps)
 {
     SSB_REQUIRE(M > 0 && rows > 0 && reps > 0, "bad arguments");
-    reserve_workspace(rows, 2);
+    Lane& L = lane(0);
+    reserve_workspace(L, rows, 2);
     const bool tc = path == 2;
     SSB_REQUIRE(!tc || (sizeof(T) == 4 && tc_supported(Npad, Mp)), "tcgen05 contraction unavailable for this dtype/shape");
     dev_buffer dP;
     dP.reserve(rows * M * sizeof(T));
-    SSB_CUDA(cudaMemcpyAsync(dP.p, P, rows * M * sizeof(T), cudaMemcpyHostToDevice, stream));
+    SSB_CUDA(cudaMemcpyAsync(dP.p, P, rows * M * sizeof(T), cudaMemcpyHostToDevice, L.stream));
     const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
-    stage_signals_kernel<T><<<blocks, 256, 0, stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, P_[0].template as<T>(),
-                                                       tc ? Plo_[0].template as<T>() : nullptr, Mp, tc ? 1 : 0);
+    stage_signals_kernel<T><<<blocks, 256, 0, L.stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, L.P[0].template as<T>(),
+                                                         tc ? L.Plo[0].template as<T>() : nullptr, Mp, tc ? 1 : 0);
     SSB_CUDA(cudaGetLastError());
-    contract(tc, 0, rows, stream);   // warm-up + the result
-    cudaEvent_t e0 = get_event(), e1 = get_event();
-    SSB_CUDA(cudaEventRecord(e0, stream));
-    for (int i = 0; i < reps; ++i) contract(tc, 0, rows, stream);
-    SSB_CUDA(cudaEventRecord(e1, stream));
-    SSB_CUDA(cudaMemcpy2DAsync(Q, N * sizeof(T), Q_.p, Npad * sizeof(T), N * sizeof(T), rows, cudaMemcpyDeviceToHost, stream));
-    SSB_CUDA(cudaStreamSynchronize(stream));
-    float ms = 0.f;
-    SSB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    event_pool.push_back(e0); event_pool.push_back(e1);
-    collect_spans();
-    return (double)ms / reps;
+    contract(L, tc, 0, rows);   // warm-up + the result
+    cudaEvent_t e0 = L.event(), e1 = L.event();
+    SSB_CUDA(cudaEventRecord(e0, L.stream));
+    for (int i = 0; i < reps; ++i) contract(L, tc, 0, rows);
+    SSB_CUDA(cudaEventRecord(e1, L.stream));
+    SSB_CUDA(cudaMemcpy2DAsync(Q, N * sizeof(T), L.Q.p, Npad * sizeof(T), N * sizeof(T), rows, cudaMemcpyDeviceToHost, L.stream));
+    SSB_CUDA(cudaStreamSynchronize(L.stream));
+    float t = 0.f;
+    SSB_CUDA(cudaEventElapsedTime(&t, e0, e1));
+    L.pool.push_back(e0); L.pool.push_back(e1);
+    merge(L);
+    return (double)t / reps;
 }
 
 template <typename T>
@@ -242,7 +367,7 @@ void Homotopy<T>::reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, s
     dX.reserve(batch * N * sizeof(T));
     dY.reserve(batch * M * sizeof(T));
     SSB_CUDA(cudaMemcpy2DAsync(dX.p, N * sizeof(T), X, ldx * sizeof(T), N * sizeof(T), batch, cudaMemcpyHostToDevice, stream));
-    reconstruct_kernel<T><<<(unsigned)batch, 128, 0, stream>>>(At_.as<T>(), Mp, M, N, dX.as<T>(), N, dY.as<T>(), M);
+    reconstruct_kernel<T><<<(unsigned)batch, 128, 0, stream>>>(At_, Mp, M, N, dX.as<T>(), N, dY.as<T>(), M);
     SSB_CUDA(cudaGetLastError());
     counters[0]++;
     SSB_CUDA(cudaMemcpy2DAsync(Y, ldy * sizeof(T), dY.p, M * sizeof(T), M * sizeof(T), batch, cudaMemcpyDeviceToHost, stream));

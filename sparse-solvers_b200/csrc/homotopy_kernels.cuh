@@ -179,6 +179,31 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
     write_rhs<T, THREADS>(a, s, s_gam, s_d, 1);
 }
 
+// out[r] = sum_k G[r][k] v[k] for the K x K inverse (the reference's K x K xgemv, homotopy-cpu.cpp:263 and
+// online_inverse.h:225).  On chip: one thread per row, k in order (odd row stride: conflict-free); in HBM: one
+// warp per row so that the loads coalesce.
+template <typename T, int THREADS, bool ON_CHIP>
+__device__ __forceinline__ void matvec(const T* G, int ld, int K, const T* v, T* out, T* out2)
+{
+    if constexpr (ON_CHIP) {
+        for (int r = threadIdx.x; r < K; r += THREADS) {
+            T acc = T(0);
+            const T* row = G + (size_t)r * ld;
+            for (int k = 0; k < K; ++k) acc += row[k] * v[k];
+            out[r] = acc;
+            if (out2) out2[r] = acc;
+        }
+    } else {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int r = warp; r < K; r += THREADS / 32) {
+            T acc = T(0);
+            for (int k = lane; k < K; k += 32) acc += G[(size_t)r * ld + k] * v[k];
+            acc = warp_sum(acc);
+            if (lane == 0) { out[r] = acc; if (out2) out2[r] = acc; }
+        }
+    }
+}
+
 // One homotopy iteration for one signal (homotopy-cpu.cpp:236-272).
 //
 // Latency is what bounds this kernel (profiles/r1_ncu_step_and_contract_v1.txt: long-scoreboard + barrier stalls, DRAM
@@ -240,10 +265,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     const T lam = a.lam[s];
     for (int k = tid; k < kb; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }   // K <= kb = min(it, Kmax)
     if constexpr (GS) {
-        for (int e = tid; e < kb * kb; e += THREADS) {
-            const int r = e / kb, k = e - r * kb;
-            s_G[r * ks + k] = Ginv[(size_t)r * a.Kmax + k];
-        }
+        for (int r = warp; r < kb; r += NW)
+            for (int k = lane; k < kb; k += 32) s_G[r * ks + k] = Ginv[(size_t)r * a.Kmax + k];
     }
     for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
     __syncthreads();
@@ -364,20 +387,15 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     // ---- toggle idx and update inv = (A_G^T A_G)^-1 (inverse_add_or_remove, :166-183)
     if (!present) {
         // online_inverse.h:203-249 (bordering); the new atom takes slot K
-        for (int r = warp; r < K; r += NW) {                                                  // u2 = inv u1
-            T acc = T(0);
-            for (int k = lane; k < K; k += 32) acc += Gm[(size_t)r * ldm + k] * s_u1[k];
-            acc = warp_sum(acc);
-            if (lane == 0) s_u2[r] = acc;
-        }
+        matvec<T, THREADS, GS>(Gm, ldm, K, s_u1, s_u2, nullptr);                               // u2 = inv u1
         __syncthreads();
         T uu = T(0);
         for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
         uu = warp_sum(uu);
         const T dd = T(1) / (dot - uu);                                                       // :228
-        for (int e = tid; e < K * K; e += THREADS) {                                          // inv += d u2 u2^T
-            const int r = e / K, k = e - r * K;
-            Gm[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
+        for (int r = warp; r < K; r += NW) {                                                  // inv += d u2 u2^T
+            const T ur = dd * s_u2[r];
+            for (int k = lane; k < K; k += 32) Gm[(size_t)r * ldm + k] += ur * s_u2[k];
         }
         for (int r = tid; r < K; r += THREADS) {                                              // border -d u2, corner d
             const T u3 = -dd * s_u2[r];
@@ -392,9 +410,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         const T sc = -(T(1) / dd);
         for (int r = tid; r < K; r += THREADS) s_u1[r] = Gm[(size_t)r * ldm + j] * sc;         // u = -col/d
         __syncthreads();
-        for (int e = tid; e < K * K; e += THREADS) {                                          // inv -= d u u^T
-            const int r = e / K, k = e - r * K;
-            if (r != j && k != j) Gm[(size_t)r * ldm + k] += (-dd * s_u1[r]) * s_u1[k];
+        for (int r = warp; r < K; r += NW) {                                                  // inv -= d u u^T
+            if (r == j) continue;
+            const T ur = -dd * s_u1[r];
+            for (int k = lane; k < K; k += 32) if (k != j) Gm[(size_t)r * ldm + k] += ur * s_u1[k];
         }
         __syncthreads();
         const int last = K - 1;
@@ -414,17 +433,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     // ---- d_G = inv * sign(c_G, tol) (:259-263); the tolerance is also the sign dead-band
     for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(s_cg[k], a.tol);
     __syncthreads();
-    for (int r = warp; r < Knew; r += NW) {
-        T acc = T(0);
-        for (int k = lane; k < Knew; k += 32) acc += Gm[(size_t)r * ldm + k] * s_cg[k];
-        acc = warp_sum(acc);
-        if (lane == 0) { s_d[r] = acc; dG[r] = acc; }
-    }
+    matvec<T, THREADS, GS>(Gm, ldm, Knew, s_cg, s_d, dG);
     if constexpr (GS) {   // the updated inverse goes back to HBM for the next iteration
-        for (int e = tid; e < Knew * Knew; e += THREADS) {
-            const int r = e / Knew, k = e - r * Knew;
-            Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
-        }
+        for (int r = warp; r < Knew; r += NW)
+            for (int k = lane; k < Knew; k += 32) Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
     }
     const T lam_new = sh_lam;
     const bool cont = (a.it < a.max_iter) && (lam_new > a.tol);   // :272
