@@ -1,0 +1,185 @@
+// Drop-in replacement for the policy section of the reference's src/lib.cpp (lines 26-112): the four
+// Policy::run overloads, the IRLS state, reconstruct_signal and norm_l1, implemented over the C ABI of
+// libssb200 (include/ssb200.h) instead of kernelpp::run<solve_*> + OpenBLAS.  Compiled against the
+// reference's UNCHANGED public headers (include/ss/*.h); nothing else of the reference is linked.
+//
+// The reference's homotopy state is a non-owning view of A (include/ss/policies.h:42) and `run` is static,
+// so the device handle lives in a small cache keyed by the view (pointer, shape, strides, dtype) and is
+// refreshed when the bytes behind the view change (the reference bench edits A between solves,
+// src/solvers/homotopy_bench.cpp:38-48).
+#include <ss/ss.h>
+
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <tuple>
+
+#include "ssb200.h"
+
+namespace {
+
+template <typename R>
+kernelpp::maybe<R> fail(int status)
+{
+    // same wording a kernelpp dispatch failure produced (kernelpp/kernel.h:122-133)
+    return kernelpp::maybe<R>{ kernelpp::error{ ssb200_status_string(status) } };
+}
+
+template <typename T> struct abi;
+template <> struct abi<float> {
+    static constexpr auto create = ssb200_homotopy_create_f32;
+    static constexpr auto refresh = ssb200_homotopy_refresh_f32;
+    static constexpr auto solve = ssb200_homotopy_solve_f32;
+    static constexpr auto irls_create = ssb200_irls_create_f32;
+    static constexpr auto irls_solve = ssb200_irls_solve_f32;
+    static constexpr auto reconstruct = ssb200_reconstruct_batch_f32;
+    static constexpr auto norm_l1 = ssb200_norm_l1_f32;
+};
+template <> struct abi<double> {
+    static constexpr auto create = ssb200_homotopy_create_f64;
+    static constexpr auto refresh = ssb200_homotopy_refresh_f64;
+    static constexpr auto solve = ssb200_homotopy_solve_f64;
+    static constexpr auto irls_create = ssb200_irls_create_f64;
+    static constexpr auto irls_solve = ssb200_irls_solve_f64;
+    static constexpr auto reconstruct = ssb200_reconstruct_batch_f64;
+    static constexpr auto norm_l1 = ssb200_norm_l1_f64;
+};
+
+template <typename Span> const typename Span::value_type* base(const Span& s) { return s.raw_data() + s.raw_data_offset(); }
+template <typename Span> ptrdiff_t stride(const Span& s, size_t d) { return (ptrdiff_t)s.strides()[d]; }
+
+// FNV-1a over the elements the view covers
+template <typename T>
+uint64_t view_hash(const ss::ndspan<T, 2>& A)
+{
+    uint64_t h = 1469598103934665603ull;
+    const T* p = base(A);
+    const size_t m = A.shape()[0], n = A.shape()[1];
+    const ptrdiff_t rs = stride(A, 0), cs = stride(A, 1);
+    for (size_t i = 0; i < m; ++i)
+        for (size_t j = 0; j < n; ++j) {
+            uint64_t bits = 0;
+            std::memcpy(&bits, p + (ptrdiff_t)i * rs + (ptrdiff_t)j * cs, sizeof(T));
+            h = (h ^ bits) * 1099511628211ull;
+        }
+    return h;
+}
+
+struct cached { void* handle = nullptr; uint64_t hash = 0; };
+using key_t = std::tuple<const void*, size_t, size_t, ptrdiff_t, ptrdiff_t, int>;
+std::map<key_t, cached> g_cache;
+std::mutex g_mu;
+
+template <typename T>
+int homotopy_handle(const ss::ndspan<T, 2>& A, void** out)
+{
+    std::lock_guard<std::mutex> g(g_mu);
+    const key_t key{ base(A), A.shape()[0], A.shape()[1], stride(A, 0), stride(A, 1), (int)sizeof(T) };
+    cached& c = g_cache[key];
+    const uint64_t h = view_hash(A);
+    if (!c.handle) {
+        if (g_cache.size() > 16) {   // keep the cache small: drop everything else
+            for (auto it = g_cache.begin(); it != g_cache.end();) {
+                if (it->first != key) { ssb200_destroy(it->second.handle); it = g_cache.erase(it); } else ++it;
+            }
+        }
+        int st = abi<T>::create(base(A), A.shape()[0], A.shape()[1], stride(A, 0), stride(A, 1), 0, &g_cache[key].handle);
+        if (st) { g_cache.erase(key); return st; }
+        g_cache[key].hash = h;
+    } else if (c.hash != h) {
+        int st = abi<T>::refresh(c.handle, base(A), stride(A, 0), stride(A, 1));
+        if (st) return st;
+        c.hash = h;
+    }
+    *out = g_cache[key].handle;
+    return 0;
+}
+
+template <typename T>
+kernelpp::maybe<ss::homotopy_report> run_homotopy(const ss::ndspan<T, 2>& A, const ss::ndspan<T> y, T tol,
+                                                  uint32_t max_iter, ss::ndspan<T> x)
+{
+    void* h = nullptr;
+    if (int st = homotopy_handle(A, &h)) return fail<ss::homotopy_report>(st);
+    ss::homotopy_report r{};
+    if (int st = abi<T>::solve(h, base(y), stride(y, 0), tol, max_iter, const_cast<T*>(base(x)), stride(x, 0),
+                               &r.iter, &r.solution_error))
+        return fail<ss::homotopy_report>(st);
+    return r;
+}
+
+struct irls_handle {
+    void* h = nullptr;
+    int status = 0;
+    ~irls_handle() { ssb200_destroy(h); }
+};
+
+template <typename T>
+std::shared_ptr<irls_handle> make_irls(const ss::ndspan<T, 2> A)
+{
+    auto p = std::make_shared<irls_handle>();
+    p->status = abi<T>::irls_create(base(A), A.shape()[0], A.shape()[1], stride(A, 0), stride(A, 1), 0, &p->h);
+    return p;
+}
+
+template <typename T>
+kernelpp::maybe<ss::irls_report> run_irls(ss::irls_state& s, const ss::ndspan<T> y, T tol, uint32_t max_iter, ss::ndspan<T> x)
+{
+    auto& p = xtl::any_cast<std::shared_ptr<irls_handle>&>(s.QR);
+    if (p->status) return fail<ss::irls_report>(p->status);
+    ss::irls_report r{};
+    uint8_t spd = 0;
+    if (int st = abi<T>::irls_solve(p->h, base(y), stride(y, 0), tol, max_iter, const_cast<T*>(base(x)), stride(x, 0),
+                                    &r.iter, &r.solution_error, &spd))
+        return fail<ss::irls_report>(st);
+    r.spd_failure = spd != 0;
+    return r;
+}
+
+template <typename T>
+void reconstruct(const ss::ndspan<T, 2> A, const ss::ndspan<T> x, ss::ndspan<T> y)
+{
+    void* h = nullptr;
+    if (homotopy_handle(A, &h)) return;
+    std::vector<T> xx(x.size()), yy(y.size());
+    for (size_t j = 0; j < xx.size(); ++j) xx[j] = base(x)[(ptrdiff_t)j * stride(x, 0)];
+    abi<T>::reconstruct(h, xx.data(), 1, xx.size(), yy.data(), yy.size());
+    for (size_t i = 0; i < yy.size(); ++i) const_cast<T*>(base(y))[(ptrdiff_t)i * stride(y, 0)] = yy[i];
+}
+
+}  // namespace
+
+namespace ss {
+
+kernelpp::maybe<homotopy_report> homotopy_policy::run(state_type<float>& A, const ndspan<float> y, float tol,
+                                                      uint32_t max_iter, ndspan<float> x)
+{ return run_homotopy<float>(A, y, tol, max_iter, x); }
+kernelpp::maybe<homotopy_report> homotopy_policy::run(state_type<double>& A, const ndspan<double> y, double tol,
+                                                      uint32_t max_iter, ndspan<double> x)
+{ return run_homotopy<double>(A, y, tol, max_iter, x); }
+homotopy_policy::homotopy_policy() = default;
+homotopy_policy::homotopy_policy(homotopy_policy&&) = default;
+homotopy_policy::~homotopy_policy() = default;
+
+irls_state::irls_state(const ndspan<float, 2> A) : QR{ make_irls<float>(A) } {}
+irls_state::irls_state(const ndspan<double, 2> A) : QR{ make_irls<double>(A) } {}
+irls_state::~irls_state() = default;
+
+kernelpp::maybe<irls_report> irls_policy::run(state_type<float>& s, const ndspan<float> y, float tol, uint32_t max_iter,
+                                              ndspan<float> x)
+{ return run_irls<float>(s, y, tol, max_iter, x); }
+kernelpp::maybe<irls_report> irls_policy::run(state_type<double>& s, const ndspan<double> y, double tol, uint32_t max_iter,
+                                              ndspan<double> x)
+{ return run_irls<double>(s, y, tol, max_iter, x); }
+
+void reconstruct_signal(const ndspan<float, 2> A, const ndspan<float> x, ndspan<float> y) { reconstruct<float>(A, x, y); }
+void reconstruct_signal(const ndspan<double, 2> A, const ndspan<double> x, ndspan<double> y) { reconstruct<double>(A, x, y); }
+void norm_l1(ndspan<float, 2> A)
+{ abi<float>::norm_l1(const_cast<float*>(base(A)), A.shape()[0], A.shape()[1], stride(A, 0), stride(A, 1), 0); }
+void norm_l1(ndspan<double, 2> A)
+{ abi<double>::norm_l1(const_cast<double*>(base(A)), A.shape()[0], A.shape()[1], stride(A, 0), stride(A, 1), 0); }
+
+}  // namespace ss

@@ -144,7 +144,7 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
         else    launch_step_variant<T, TH, NC, false>(grid, smem, st, a, kb, ks);                 \
         return;                                                                                   \
     }
-    SSB_STEP(128, 1) SSB_STEP(128, 2) SSB_STEP(128, 4) SSB_STEP(256, 4) SSB_STEP(256, 0)
+    SSB_STEP(128, 1) SSB_STEP(128, 2) SSB_STEP(128, 4) SSB_STEP(256, 1) SSB_STEP(256, 2) SSB_STEP(256, 4) SSB_STEP(256, 0)
 #undef SSB_STEP
     throw invalid_argument{ "no step-kernel variant for this shape" };
 }
@@ -189,8 +189,11 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     // step-kernel variant: c,q register-resident when the dictionary is narrow enough, inverse on chip when it fits
     constexpr int V = 16 / sizeof(T);
     const int chunks128 = (Npad + 128 * V - 1) / (128 * V), chunks256 = (Npad + 256 * V - 1) / (256 * V);
-    const int threads = chunks128 <= 4 ? 128 : 256;
-    const int nch = chunks128 <= 1 ? 1 : chunks128 <= 2 ? 2 : chunks128 <= 4 ? 4 : chunks256 <= 4 ? 4 : 0;
+    int threads = chunks128 <= 4 ? 128 : 256;
+    int nch = chunks128 <= 1 ? 1 : chunks128 <= 2 ? 2 : chunks128 <= 4 ? 4 : chunks256 <= 4 ? 4 : 0;
+    if (const char* e = getenv("SSB200_STEP_THREADS")) if (atoi(e) == 256) {                          // tuning knob
+        threads = 256; nch = chunks256 <= 1 ? 1 : chunks256 <= 2 ? 2 : chunks256 <= 4 ? 4 : 0;
+    }
     const size_t g_budget = 96 * 1024;
 
     size_t count = rows;
