@@ -102,7 +102,13 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def window(self, t0, t1):
+        """keep the samples taken inside the timed region (the sampler is started before the warm-up: the first
+        nvidia-smi query on a fresh box takes seconds and stalls CUDA calls while it initialises)"""
+        inside = [r for t, r in self.rows if t0 <= t <= t1]
+        self.rows = inside if inside else [r for _, r in self.rows[-3:]]
 
     def stop(self):
         if not self.proc:
@@ -112,6 +118,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
+        self.rows = [r[1] if isinstance(r, tuple) else r for r in self.rows]
         sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
         if not sm:
             return None
@@ -216,20 +223,23 @@ def run_b200(args, cfg):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(args.warmup):
         step_dev()
     solver.reset_counters()
     solver.set_timing(True)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     barrier()
+    t_wall0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step_dev()
     e1.record()
     barrier()
+    if rank == 0:
+        sampler.window(t_wall0, time.perf_counter())
     clocks = sampler.stop() if rank == 0 else None
     ms = e0.elapsed_time(e1)
     solver.set_timing(False)

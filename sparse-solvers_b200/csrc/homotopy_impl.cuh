@@ -165,6 +165,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     a.iters = d_iters; a.errs = d_errs;
     a.split = tc ? 1 : 0;
     a.tol = tol; a.max_iter = max_iter;
+    if (const char* e = getenv("SSB200_DBG")) a.dbg = atoi(e);
 
     // c0 = A^T y for the whole chunk (homotopy-cpu.cpp:215)
     {

@@ -53,6 +53,7 @@ struct HomArgs {
     T tol;
     uint32_t max_iter;
     uint32_t it;      // lockstep iteration number, 1-based
+    int dbg;          // timing experiments only (SSB200_DBG): 1 = stop after the c update, 2 = stop before p
 };
 
 __device__ __forceinline__ float tf32_rna(float x) {
@@ -265,8 +266,23 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     const T lam = a.lam[s];
     for (int k = tid; k < kb; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }   // K <= kb = min(it, Kmax)
     if constexpr (GS) {
-        for (int r = warp; r < kb; r += NW)
-            for (int k = lane; k < kb; k += 32) s_G[r * ks + k] = Ginv[(size_t)r * a.Kmax + k];
+        // flat copy, 8 independent loads in flight per thread (row = e / kb by multiply-high: exact for e*kb < 2^32)
+        const uint32_t total = (uint32_t)(kb * kb), magic = (uint32_t)((0x100000000ull + kb - 1) / kb);
+        for (uint32_t e0 = tid; e0 < total; e0 += 8 * THREADS) {
+            T v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t e = e0 + u * THREADS;
+                const uint32_t r = __umulhi(e, magic);
+                if (e < total) v[u] = Ginv[(size_t)r * a.Kmax + (e - r * kb)];
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t e = e0 + u * THREADS;
+                const uint32_t r = __umulhi(e, magic);
+                if (e < total) s_G[r * ks + (e - r * kb)] = v[u];
+            }
+        }
     }
     for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
     __syncthreads();
@@ -384,6 +400,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     // inverse is being updated
     for (int k = tid; k < K + (present ? 0 : 1); k += THREADS) s_cg[k] = __ldcg(c + (k < K ? s_gam[k] : idx));
 
+    if (a.dbg == 1) { if (tid == 0) { const int row = atomicAdd(a.next_count, 1); a.act_next[row] = s; } return; }
     // ---- toggle idx and update inv = (A_G^T A_G)^-1 (inverse_add_or_remove, :166-183)
     if (!present) {
         // online_inverse.h:203-249 (bordering); the new atom takes slot K
@@ -453,7 +470,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         }
     }
     __syncthreads();
-    if (cont) write_rhs<T, THREADS>(a, sh_row, s_gam, s_d, Knew);
+    if (cont && a.dbg != 2) write_rhs<T, THREADS>(a, sh_row, s_gam, s_d, Knew);
 }
 
 // dynamic shared memory of the step kernel: per-slot vectors, membership mask, and (when held on chip) the inverse
