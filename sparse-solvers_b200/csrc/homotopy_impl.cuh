@@ -216,6 +216,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const bool gs = (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
         const size_t smem = homotopy_step_smem<T>(L.ws_kmax, Npad, gs ? kb + 1 : 0, ks);
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
+        SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
         const int span = L.begin(timing, 1);
         launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
         L.end(span);

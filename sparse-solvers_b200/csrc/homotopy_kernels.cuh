@@ -95,6 +95,12 @@ __global__ void stage_signals_kernel(const T* __restrict__ Y, size_t ldy, int M,
     }
 }
 
+// join-candidate step (lambda -+ c_i) / (1 -+ q_i) (homotopy-cpu.cpp:143-153).  2N of these per signal-iteration make
+// the IEEE division sequence the largest single consumer of issue slots in the step kernel, so float32 uses the
+// hardware reciprocal (<= 2 ulp; c and q already carry more rounding than that, exact cases such as x/1 stay exact).
+__device__ __forceinline__ float step_ratio(float num, float den) { return __fdividef(num, den); }
+__device__ __forceinline__ double step_ratio(double num, double den) { return num / den; }
+
 template <typename T>
 __device__ __forceinline__ T sign_tol(T v, T tol) { return v > tol ? T(1) : (v < -tol ? T(-1) : T(0)); }
 
@@ -262,6 +268,21 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             }
         }
     }
+    if constexpr (NCH > 0) {
+        if (a.dbg == 3) {   // timing experiment: pure c/q streaming
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                const int i0 = (ch * THREADS + tid) * V;
+                if (i0 < a.ldc) {
+#pragma unroll
+                    for (int e = 0; e < V; ++e) cv[ch][e] -= T(0.5) * qv[ch][e];
+                    *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(cv[ch]);
+                }
+            }
+            if (tid == 0) { const int row = atomicAdd(a.next_count, 1); a.act_next[row] = s; }
+            return;
+        }
+    }
     const int K = a.Kcur[s];
     const T lam = a.lam[s];
     for (int k = tid; k < kb; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }   // K <= kb = min(it, Kmax)
@@ -286,10 +307,18 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     }
     for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
     __syncthreads();
-    for (int k = tid; k < K; k += THREADS) {
-        const uint32_t g = s_gam[k];
-        atomicOr(&mask[g >> 5], 1u << (g & 31));
-        s_x[k] = x[g];
+    // per-slot values stay in registers (slot k lives in thread k % THREADS) so that no load is waited for
+    // before its value is needed: x at the active atoms, the Gram row of a joining atom, c at the active atoms
+    constexpr int KR = 3;   // K <= KR * THREADS (checked by the host)
+    T xk[KR], u1r[KR], cgr[KR];
+#pragma unroll
+    for (int u = 0; u < KR; ++u) {
+        const int k = tid + u * THREADS;
+        if (k < K) {
+            const uint32_t g = s_gam[k];
+            atomicOr(&mask[g >> 5], 1u << (g & 31));
+            xk[u] = x[g];
+        }
     }
     __syncthreads();
 
@@ -303,8 +332,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             const int i = i0 + e;
             if (i < a.N && !((mw >> e) & 1u)) {
                 const T dl = T(1) - qq[e], dr = T(1) + qq[e];
-                if (dl != T(0)) { const T t = (lam - cc[e]) / dl; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
-                if (dr != T(0)) { const T t = (lam + cc[e]) / dr; if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                if (dl != T(0)) { const T t = step_ratio(lam - cc[e], dl); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                if (dr != T(0)) { const T t = step_ratio(lam + cc[e], dr); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
             }
         }
     };
@@ -322,10 +351,14 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             scan(cc, qq, i0);
         }
     }
-    for (int k = tid; k < K; k += THREADS) {   // leave candidates, -x_i / d_i (:129-137)
-        const uint32_t i = s_gam[k];
-        const T t = -s_x[k] / s_d[k];
-        if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
+#pragma unroll
+    for (int u = 0; u < KR; ++u) {   // leave candidates, -x_i / d_i (:129-137)
+        const int k = tid + u * THREADS;
+        if (k < K) {
+            const uint32_t i = s_gam[k];
+            const T t = -xk[u] / s_d[k];
+            if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
+        }
     }
     warp_argmin(best, bidx);
     if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
@@ -357,12 +390,20 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     // ---- loads that depend on idx, issued before the streaming update so their latency is hidden
     T dot = T(0);
     if (!present) {
-        for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];   // u1 = A_G^T v (online_inverse.h:218)
+#pragma unroll
+        for (int u = 0; u < KR; ++u) {                                                         // u1 = A_G^T v (online_inverse.h:218)
+            const int k = tid + u * THREADS;
+            if (k < K) u1r[u] = a.G[(size_t)idx * a.ldg + s_gam[k]];
+        }
         dot = a.G[(size_t)idx * a.ldg + idx];                                                 // v.v
     }
 
     // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
-    for (int k = tid; k < K; k += THREADS) x[s_gam[k]] = s_x[k] + gamma * s_d[k];
+#pragma unroll
+    for (int u = 0; u < KR; ++u) {
+        const int k = tid + u * THREADS;
+        if (k < K) x[s_gam[k]] = xk[u] + gamma * s_d[k];
+    }
 
     // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
     T mx = T(0);
@@ -390,6 +431,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     }
     mx = warp_max(mx);
     if (lane == 0) red_v[warp] = mx;
+    if (!present) {
+#pragma unroll
+        for (int u = 0; u < KR; ++u) { const int k = tid + u * THREADS; if (k < K) s_u1[k] = u1r[u]; }
+    }
     __syncthreads();   // also orders sh_slot, s_u1 and the c stores
     if (tid == 0) {
         T m = red_v[0];
@@ -398,7 +443,12 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     }
     // c at the (old-slot) active atoms and at a joining atom, for the signs; read back through L2 while the
     // inverse is being updated
-    for (int k = tid; k < K + (present ? 0 : 1); k += THREADS) s_cg[k] = __ldcg(c + (k < K ? s_gam[k] : idx));
+    const int ncg = K + (present ? 0 : 1);
+#pragma unroll
+    for (int u = 0; u < KR; ++u) {
+        const int k = tid + u * THREADS;
+        if (k < ncg) cgr[u] = __ldcg(c + (k < K ? s_gam[k] : idx));
+    }
 
     if (a.dbg == 1) { if (tid == 0) { const int row = atomicAdd(a.next_count, 1); a.act_next[row] = s; } return; }
     // ---- toggle idx and update inv = (A_G^T A_G)^-1 (inverse_add_or_remove, :166-183)
@@ -420,6 +470,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             Gm[(size_t)K * ldm + r] = u3;
         }
         if (tid == 0) { Gm[(size_t)K * ldm + K] = dd; s_gam[K] = idx; gam[K] = idx; }
+#pragma unroll
+        for (int u = 0; u < KR; ++u) { const int k = tid + u * THREADS; if (k < ncg) s_cg[k] = cgr[u]; }
     } else {
         // online_inverse.h:253-293; the leaving atom sits in slot j
         const int j = sh_slot;
@@ -432,6 +484,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             const T ur = -dd * s_u1[r];
             for (int k = lane; k < K; k += 32) if (k != j) Gm[(size_t)r * ldm + k] += ur * s_u1[k];
         }
+#pragma unroll
+        for (int u = 0; u < KR; ++u) { const int k = tid + u * THREADS; if (k < ncg) s_cg[k] = cgr[u]; }
         __syncthreads();
         const int last = K - 1;
         if (j != last) {   // refill slot j with the last slot (reads touch row/col `last` only, writes never do)
