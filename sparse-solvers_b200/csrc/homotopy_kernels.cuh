@@ -325,15 +325,37 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index
     T best = TMAX;
     uint32_t bidx = 0xffffffffu;
+    // float32: candidates are compared as integer keys bits(t) - 1, unsigned: the order of positive floats, while
+    // zero, negatives, inf and NaN all land above bits(FLT_MAX) - 1 and lose -- one min per candidate instead of
+    // two compares and two selects, and the (rare) new minimum is located afterwards.
+    uint32_t bestkey = __float_as_uint(FLT_MAX) - 1u;
     auto scan = [&](const T (&cc)[V], const T (&qq)[V], int i0) {
         const uint32_t mw = mask[i0 >> 5] >> (i0 & 31);
+        if constexpr (sizeof(T) == 4) {
+            uint32_t key[V];
 #pragma unroll
-        for (int e = 0; e < V; ++e) {
-            const int i = i0 + e;
-            if (i < a.N && !((mw >> e) & 1u)) {
-                const T dl = T(1) - qq[e], dr = T(1) + qq[e];
-                if (dl != T(0)) { const T t = step_ratio(lam - cc[e], dl); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
-                if (dr != T(0)) { const T t = step_ratio(lam + cc[e], dr); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+            for (int e = 0; e < V; ++e) {
+                const float t1 = step_ratio(lam - cc[e], 1.0f - qq[e]), t2 = step_ratio(lam + cc[e], 1.0f + qq[e]);
+                const uint32_t k12 = min(__float_as_uint(t1) - 1u, __float_as_uint(t2) - 1u);
+                key[e] = ((mw >> e) & 1u) || (i0 + e >= a.N) ? 0xffffffffu : k12;
+            }
+            uint32_t m = key[0];
+#pragma unroll
+            for (int e = 1; e < V; ++e) m = min(m, key[e]);
+            if (m < bestkey) {
+                bestkey = m;
+#pragma unroll
+                for (int e = V - 1; e >= 0; --e) if (key[e] == m) bidx = (uint32_t)(i0 + e);
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const int i = i0 + e;
+                if (i < a.N && !((mw >> e) & 1u)) {
+                    const T dl = T(1) - qq[e], dr = T(1) + qq[e];
+                    if (dl != T(0)) { const T t = step_ratio(lam - cc[e], dl); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                    if (dr != T(0)) { const T t = step_ratio(lam + cc[e], dr); if (t > T(0) && t < best) { best = t; bidx = (uint32_t)i; } }
+                }
             }
         }
     };
@@ -351,6 +373,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             scan(cc, qq, i0);
         }
     }
+    if constexpr (sizeof(T) == 4) best = bidx == 0xffffffffu ? TMAX : __uint_as_float(bestkey + 1u);
 #pragma unroll
     for (int u = 0; u < KR; ++u) {   // leave candidates, -x_i / d_i (:129-137)
         const int k = tid + u * THREADS;
@@ -460,9 +483,12 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
         uu = warp_sum(uu);
         const T dd = T(1) / (dot - uu);                                                       // :228
-        for (int r = warp; r < K; r += NW) {                                                  // inv += d u2 u2^T
-            const T ur = dd * s_u2[r];
-            for (int k = lane; k < K; k += 32) Gm[(size_t)r * ldm + k] += ur * s_u2[k];
+        {                                                                                     // inv += d u2 u2^T
+            const uint32_t total = (uint32_t)(K * K), magic = (uint32_t)((0x100000000ull + K - 1) / K);
+            for (uint32_t e = tid; e < total; e += THREADS) {
+                const uint32_t r = __umulhi(e, magic), k = e - r * K;
+                Gm[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
+            }
         }
         for (int r = tid; r < K; r += THREADS) {                                              // border -d u2, corner d
             const T u3 = -dd * s_u2[r];
@@ -506,8 +532,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     __syncthreads();
     matvec<T, THREADS, GS>(Gm, ldm, Knew, s_cg, s_d, dG);
     if constexpr (GS) {   // the updated inverse goes back to HBM for the next iteration
-        for (int r = warp; r < Knew; r += NW)
-            for (int k = lane; k < Knew; k += 32) Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
+        const uint32_t total = (uint32_t)(Knew * Knew), magic = (uint32_t)((0x100000000ull + Knew - 1) / Knew);
+        for (uint32_t e = tid; e < total; e += THREADS) {
+            const uint32_t r = __umulhi(e, magic), k = e - r * Knew;
+            Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
+        }
     }
     const T lam_new = sh_lam;
     const bool cont = (a.it < a.max_iter) && (lam_new > a.tol);   // :272
