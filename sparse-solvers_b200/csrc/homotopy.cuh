@@ -14,6 +14,7 @@
 
 #include "contract_simt.cuh"
 #include "homotopy_kernels.cuh"
+#include "homotopy_split.cuh"
 #include "solver_base.h"
 
 namespace ssb {
@@ -108,7 +109,7 @@ private:
     // path, its H2D / D2H copies).
     struct Lane {
         cudaStream_t stream = nullptr;
-        dev_buffer C, Q, P[2], Plo[2], gam, dG, Ginv, lam, K, act[2], counts;
+        dev_buffer C, Q, P[2], Plo[2], gam, dG, Ginv, lam, K, pick, act[2], counts;
         dev_buffer stY, stX, stIt, stErr;     // staging for the host-pointer entry points
         pinned_buffer h_count;
         TcPlan* plan[2] = { nullptr, nullptr };

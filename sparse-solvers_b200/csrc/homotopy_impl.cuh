@@ -92,6 +92,7 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
     L.Ginv.reserve(r * (size_t)k * k * sizeof(T));
     L.lam.reserve(r * sizeof(T));
     L.K.reserve(r * sizeof(int));
+    L.pick.reserve(r * sizeof(uint32_t));
     L.counts.reserve(2 * sizeof(int));
     L.h_count.reserve(sizeof(int));
     SSB_CUDA(cudaStreamSynchronize(L.stream));
@@ -151,6 +152,41 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
 
 
 template <typename T>
+static void launch_scan(int threads, int nch, unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a)
+{
+#define SSB_SCAN(TH, NC)                                                                          \
+    if (threads == TH && nch == NC) { homotopy_scan_kernel<T, TH, NC><<<grid, TH, smem, st>>>(a); SSB_CUDA(cudaGetLastError()); return; }
+    SSB_SCAN(128, 1) SSB_SCAN(128, 2) SSB_SCAN(128, 4) SSB_SCAN(256, 1) SSB_SCAN(256, 2) SSB_SCAN(256, 4) SSB_SCAN(256, 0)
+#undef SSB_SCAN
+    throw invalid_argument{ "no scan-kernel variant for this shape" };
+}
+
+template <typename T, int W>
+static void launch_algebra_variant(unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
+{
+    static size_t configured = 0;
+    const size_t smem = slice * W;
+    if (smem > 48 * 1024 && smem > configured) {
+        SSB_CUDA(cudaFuncSetAttribute(homotopy_algebra_kernel<T, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = 200 * 1024;
+    }
+    homotopy_algebra_kernel<T, W><<<(rows + W - 1) / W, W * 32, smem, st>>>(a, kb, ks, (int)slice);
+    SSB_CUDA(cudaGetLastError());
+}
+
+// warps per CTA of the algebra kernel for a slice size; 0 = the active set is too large for the split kernels
+static inline int algebra_warps(size_t slice) { return slice <= 24 * 1024 ? 4 : slice <= 48 * 1024 ? 2 : slice <= 96 * 1024 ? 1 : 0; }
+
+template <typename T>
+static void launch_algebra(int W, unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
+{
+    if (W == 4) launch_algebra_variant<T, 4>(rows, slice, st, a, kb, ks);
+    else if (W == 2) launch_algebra_variant<T, 2>(rows, slice, st, a, kb, ks);
+    else launch_algebra_variant<T, 1>(rows, slice, st, a, kb, ks);
+}
+
+
+template <typename T>
 void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX,
                               size_t ldx, uint32_t* d_iters, double* d_errs)
 {
@@ -161,7 +197,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     a.At = At_; a.G = G_; a.ldg = Npad;
     a.C = L.C.template as<T>(); a.Q = L.Q.template as<T>(); a.X = dX; a.ldx = ldx;
     a.gam = L.gam.template as<uint32_t>(); a.dG = L.dG.template as<T>(); a.Ginv = L.Ginv.template as<T>();
-    a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>();
+    a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>(); a.pick = L.pick.template as<uint32_t>();
     a.iters = d_iters; a.errs = d_errs;
     a.split = tc ? 1 : 0;
     a.tol = tol; a.max_iter = max_iter;
@@ -196,6 +232,8 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         threads = 256; nch = chunks256 <= 1 ? 1 : chunks256 <= 2 ? 2 : chunks256 <= 4 ? 4 : 0;
     }
     const size_t g_budget = 96 * 1024;
+    bool split_ok = true;                                                                            // scan + algebra kernels
+    if (const char* e = getenv("SSB200_SPLIT")) split_ok = atoi(e) != 0;                              // tuning knob
 
     size_t count = rows;
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
@@ -217,10 +255,18 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const size_t smem = homotopy_step_smem<T>(L.ws_kmax, Npad, gs ? kb + 1 : 0, ks);
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
         SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
+        const size_t slice = homotopy_algebra_slice<T>(kb, ks);
+        const int aw = split_ok ? algebra_warps(slice) : 0;
         const int span = L.begin(timing, 1);
-        launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
+        if (aw > 0) {
+            launch_scan(threads, nch, (unsigned)count, homotopy_scan_smem<T>(L.ws_kmax, Npad), st, a);
+            launch_algebra(aw, (unsigned)count, slice, st, a, kb, ks);
+            L.counters[0] += 2;
+        } else {
+            launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
+            L.counters[0]++;
+        }
         L.end(span);
-        L.counters[0]++;
         L.counters[3]++;
         SSB_CUDA(cudaMemcpyAsync(h_count, next_count, sizeof(int), cudaMemcpyDeviceToHost, st));
         SSB_CUDA(cudaStreamSynchronize(st));

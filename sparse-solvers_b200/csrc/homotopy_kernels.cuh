@@ -47,6 +47,7 @@ struct HomArgs {
     const int* act;   // [rows]      position -> signal (nullptr: identity)
     int* act_next;    // compacted list for the next iteration
     int* next_count;
+    uint32_t* pick;   // [Bc]        atom chosen by the min-gamma search (split kernels: scan -> algebra)
     T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
     T* Pn_lo;         //             TF32 lo part (only when split != 0)
     int split;
