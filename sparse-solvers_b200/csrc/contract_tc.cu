@@ -104,12 +104,15 @@ __device__ __forceinline__ uint64_t make_desc(const void* tile) {
 }
 
 // instruction descriptor: D = F32, A = B = TF32, both K-major, M = 128, N = 256
-constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TILE_SIGS >> 3) << 17) | ((uint32_t)(TILE_ATOMS >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc(int n_sigs) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_sigs >> 3) << 17) | ((uint32_t)(TILE_ATOMS >> 4) << 24);
+}
+constexpr int THIN_SIGS = 32;       // UMMA N of the thin-tail variant (same accumulation per element, 1/8 of the tensor and TMA work)
 
 __global__ void __launch_bounds__(THREADS, 1)
 contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                        const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
-                       float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks)
+                       float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks, int tile_sigs)
 {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar, tmem_empty_bar;
@@ -141,12 +144,12 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int n0 = (tile % atom_tiles) * TILE_ATOMS;
-                const int r0 = (tile / atom_tiles) * TILE_SIGS;
+                const int r0 = (tile / atom_tiles) * tile_sigs;
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
                     const int s = it % STAGES;
                     mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
                     uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    mbar_expect_tx(&full_bar[s], 2 * A_TILE_BYTES + 2 * tile_sigs * BLOCK_K * 4);
                     tma_load_2d(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
                     tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
                     tma_load_2d(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
@@ -159,6 +162,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         if (lane == 0) {
             uint32_t it = 0, t = 0;
             const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
+            const uint32_t IDESC = make_idesc(tile_sigs);
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
                 mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -188,27 +192,31 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         uint32_t t = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
             const int n0 = (tile % atom_tiles) * TILE_ATOMS;
-            const int r0 = (tile / atom_tiles) * TILE_SIGS + half * (TILE_SIGS / 2);
+            const int r0 = (tile / atom_tiles) * tile_sigs + half * (TILE_SIGS / 2);
             mbar_wait(&tmem_full_bar, t & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
             float* qcol = Q + n0 + quarter * 32 + lane;
-#pragma unroll 1
+            // drain both accumulators into registers first and hand TMEM back: the next tile's MMAs run while
+            // this tile's stores are still in flight (with both accumulators resident TMEM cannot be double-buffered)
+            float r[TILE_SIGS / 2];
+#pragma unroll
             for (int c0 = 0; c0 < TILE_SIGS / 2; c0 += 32) {
-                if (r0 + c0 >= rows) break;                // warp-uniform
                 uint32_t v[32], w[32];
                 tmem_ld32(taddr0 + (uint32_t)c0, v);
                 tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int r = r0 + c0 + j;
-                    if (r < rows) qcol[(size_t)r * ldq] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
-                }
+                for (int j = 0; j < 32; ++j) r[c0 + j] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty_bar);
+#pragma unroll
+            for (int j = 0; j < TILE_SIGS / 2; ++j) {
+                const int rr = r0 + j;
+                if (rr < rows && half * (TILE_SIGS / 2) + j < tile_sigs) qcol[(size_t)rr * ldq] = r[j];
+            }
         }
     }
 
@@ -258,7 +266,7 @@ CUtensorMap make_map(const float* base, int inner, int outer, int box_rows)
 }  // namespace
 
 struct TcPlan {
-    CUtensorMap a_hi, a_lo, p_hi, p_lo;
+    CUtensorMap a_hi, a_lo, p_hi, p_lo, p_hi_thin, p_lo_thin;
     int n_pad, mp, rows_alloc, sms;
 };
 
@@ -273,6 +281,8 @@ TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp
         p->a_lo = make_map(At_lo, mp, n_pad, TILE_ATOMS);
         p->p_hi = make_map(P_hi, mp, rows_alloc, TILE_SIGS);
         p->p_lo = make_map(P_lo, mp, rows_alloc, TILE_SIGS);
+        p->p_hi_thin = make_map(P_hi, mp, rows_alloc, THIN_SIGS);
+        p->p_lo_thin = make_map(P_lo, mp, rows_alloc, THIN_SIGS);
     } catch (...) { delete p; throw; }
     p->n_pad = n_pad; p->mp = mp; p->rows_alloc = rows_alloc;
     int dev = 0;
@@ -289,10 +299,13 @@ void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
     if (rows <= 0) return;
     SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
     const int atom_tiles = p->n_pad / TILE_ATOMS;
-    const int sig_tiles = (rows + TILE_SIGS - 1) / TILE_SIGS;
+    const bool thin = rows <= THIN_SIGS;
+    const int tile_sigs = thin ? THIN_SIGS : TILE_SIGS;
+    const int sig_tiles = (rows + tile_sigs - 1) / tile_sigs;
     const int grid = std::min(atom_tiles * sig_tiles, p->sms);
-    contract_tf32x3_kernel<<<grid, THREADS, SMEM_BYTES, stream>>>(p->a_hi, p->a_lo, p->p_hi, p->p_lo, Q, ldq, rows,
-                                                                  atom_tiles, sig_tiles, p->mp / BLOCK_K);
+    contract_tf32x3_kernel<<<grid, THREADS, SMEM_BYTES, stream>>>(p->a_hi, p->a_lo, thin ? p->p_hi_thin : p->p_hi,
+                                                                  thin ? p->p_lo_thin : p->p_lo, Q, ldq, rows,
+                                                                  atom_tiles, sig_tiles, p->mp / BLOCK_K, tile_sigs);
     SSB_CUDA(cudaGetLastError());
 }
 

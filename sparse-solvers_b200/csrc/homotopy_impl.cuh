@@ -239,15 +239,18 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
     int* d_counts = L.counts.template as<int>();
     int* h_count = L.h_count.template as<int>();
+    bool tc_cur = tc;            // how P[cur] was written: TF32 hi/lo pair (tensor path) or full precision (SIMT path)
     for (uint32_t it = 1; it <= max_iter && count > 0; ++it) {
-        contract(L, tc, cur, count);
+        contract(L, tc_cur, cur, count);
+        const bool tc_next = tc_cur;   // (a SIMT tail would make a signal's rounding depend on the batch it travels in)
+        a.split = tc_next ? 1 : 0;
         int* next_count = d_counts + (it & 1);
         SSB_CUDA(cudaMemsetAsync(next_count, 0, sizeof(int), st));
         a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
         a.act_next = L.act[cur ^ 1].template as<int>();
         a.next_count = next_count;
         a.Pn = L.P[cur ^ 1].template as<T>();
-        a.Pn_lo = tc ? L.Plo[cur ^ 1].template as<T>() : nullptr;
+        a.Pn_lo = tc_next ? L.Plo[cur ^ 1].template as<T>() : nullptr;
         a.it = it;
         const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
         const int ks = (kb + 1) | 1;                                          // odd row stride: conflict-free column reads
@@ -256,7 +259,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
         SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
         const size_t slice = homotopy_algebra_slice<T>(kb, ks);
-        const int aw = split_ok ? algebra_warps(slice) : 0;
+        const int aw = (split_ok && count >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
         if (aw > 0) {
             launch_scan(threads, nch, (unsigned)count, homotopy_scan_smem<T>(L.ws_kmax, Npad), st, a);
@@ -272,6 +275,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_CUDA(cudaStreamSynchronize(st));
         count = (size_t)*h_count;
         cur ^= 1;
+        tc_cur = tc_next;
     }
     SSB_CUDA(cudaStreamSynchronize(st));
 }
