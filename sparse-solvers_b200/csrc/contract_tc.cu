@@ -28,9 +28,16 @@ namespace {
 
 constexpr int TILE_ATOMS = 128;     // UMMA M
 constexpr int TILE_SIGS = 256;      // UMMA N
-constexpr int BLOCK_K = 32;         // floats per K-block = 128 bytes
+// The operand stream is latency-bound, not bandwidth-bound: a stage can only be refilled after its MMAs retire, so the
+// bytes in flight are (STAGES - 1) stages.  With two 96 KB stages (BLOCK_K = 32) one stage in flight covered 70 % of
+// the tensor time; four 48 KB stages (BLOCK_K = 16, 64-byte swizzle) keep three in flight from the same shared memory.
+#ifndef SSB_BLOCK_K
+#define SSB_BLOCK_K 16
+#endif
+constexpr int BLOCK_K = SSB_BLOCK_K;   // floats per K-block: 32 = one 128-byte swizzle span, 16 = one 64-byte span
+constexpr int ROW_BYTES = BLOCK_K * 4;
 constexpr int UMMA_K = 8;           // tf32
-constexpr int STAGES = 2;
+constexpr int STAGES = BLOCK_K == 32 ? 2 : 4;
 constexpr int A_TILE_BYTES = TILE_ATOMS * BLOCK_K * 4;   // 16 KB
 constexpr int P_TILE_BYTES = TILE_SIGS * BLOCK_K * 4;    // 32 KB
 constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * P_TILE_BYTES;   // 96 KB
@@ -97,9 +104,9 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 __device__ __forceinline__ uint64_t make_desc(const void* tile) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_u32(tile) >> 4) & 0x3FFF);   // start address
-    d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset
+    d |= (uint64_t)((8 * ROW_BYTES) >> 4) << 32;       // stride byte offset: one 8-row swizzle group
     d |= (uint64_t)1 << 46;                            // descriptor version (sm_100)
-    d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
+    d |= (uint64_t)(ROW_BYTES == 128 ? 2 : 4) << 61;   // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
 
@@ -257,7 +264,7 @@ CUtensorMap make_map(const float* base, int inner, int outer, int box_rows)
     cuuint32_t box[2] = { (cuuint32_t)BLOCK_K, (cuuint32_t)box_rows };
     cuuint32_t estr[2] = { 1, 1 };
     CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, ROW_BYTES == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) throw invalid_argument{ "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")" };
     return m;
