@@ -18,6 +18,7 @@
 // Barriers: full/empty per smem stage (TMA <-> MMA), tmem_full/tmem_empty for the accumulator pair (MMA <-> epilogue).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "solver_base.h"
@@ -84,6 +85,22 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_mc(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
+// arrives on the barrier at the same offset in every CTA of `mask` once the MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_size() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -127,10 +144,16 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_tiles = atom_tiles * sig_tiles;
+    // A cluster of `cs` CTAs works on cs neighbouring atom tiles of ONE signal tile: each CTA fetches 1/cs of the
+    // P tile and multicasts it to all of them, so the signal operand crosses the L2 -> SM fabric once per cluster
+    // (the operand stream, not the tensor pipe, is what bounded the single-CTA kernel: 61 of ~64 B/clk/SM).
+    const int cs = (int)cluster_size(), crank = (int)cluster_rank();
+    const uint16_t cmask = (uint16_t)((1u << cs) - 1u);
+    const int num_items = (atom_tiles / cs) * sig_tiles;          // work items of one cluster-wide step
+    const int cluster_id = blockIdx.x / cs, num_clusters = gridDim.x / cs;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], cs); }
         mbar_init(&tmem_full_bar, 1);
         mbar_init(&tmem_empty_bar, EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -142,6 +165,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (cs > 1) cluster_sync_all();       // every CTA's barriers exist before a peer multicasts into them
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_slot;
 
@@ -149,18 +173,26 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int n0 = (tile % atom_tiles) * TILE_ATOMS;
-                const int r0 = (tile / atom_tiles) * tile_sigs;
+            const int part_rows = tile_sigs / cs;                       // rows of the P tile this CTA fetches
+            const int part_bytes = part_rows * ROW_BYTES;
+            for (int item = cluster_id; item < num_items; item += num_clusters) {
+                const int n0 = ((item % (atom_tiles / cs)) * cs + crank) * TILE_ATOMS;
+                const int r0 = (item / (atom_tiles / cs)) * tile_sigs;
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
                     const int s = it % STAGES;
-                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);      // every CTA of the cluster has drained stage s
                     uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                    mbar_expect_tx(&full_bar[s], 2 * A_TILE_BYTES + 2 * tile_sigs * BLOCK_K * 4);
+                    mbar_expect_tx(&full_bar[s], 2 * A_TILE_BYTES + 2 * tile_sigs * ROW_BYTES);
                     tma_load_2d(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
                     tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
-                    tma_load_2d(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
-                    tma_load_2d(st + 2 * A_TILE_BYTES + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                    uint8_t* ph = st + 2 * A_TILE_BYTES + crank * part_bytes;
+                    if (cs == 1) {
+                        tma_load_2d(ph, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
+                        tma_load_2d(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                    } else {
+                        tma_load_2d_mc(ph, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0 + crank * part_rows, cmask);
+                        tma_load_2d_mc(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0 + crank * part_rows, cmask);
+                    }
                 }
             }
         }
@@ -170,7 +202,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
             uint32_t it = 0, t = 0;
             const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
             const uint32_t IDESC = make_idesc(tile_sigs);
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            for (int item = cluster_id; item < num_items; item += num_clusters, ++t) {
                 mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
@@ -187,7 +219,8 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
                         umma_tf32(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
                         umma_tf32(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
                     }
-                    umma_commit(&empty_bar[s]);            // frees the smem stage when these MMAs retire
+                    if (cs == 1) umma_commit(&empty_bar[s]);   // frees the smem stage when these MMAs retire
+                    else umma_commit_mc(&empty_bar[s], cmask);  // ... in every CTA that multicasts into it
                 }
                 umma_commit(&tmem_full_bar);               // both accumulators complete
             }
@@ -197,9 +230,9 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         const int quarter = warp & 3;                      // TMEM lanes this warp may read
         const int half = (warp - 2) >> 2;                  // which 128 signal columns of the tile
         uint32_t t = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-            const int n0 = (tile % atom_tiles) * TILE_ATOMS;
-            const int r0 = (tile / atom_tiles) * tile_sigs + half * (TILE_SIGS / 2);
+        for (int item = cluster_id; item < num_items; item += num_clusters, ++t) {
+            const int n0 = ((item % (atom_tiles / cs)) * cs + crank) * TILE_ATOMS;
+            const int r0 = (item / (atom_tiles / cs)) * tile_sigs + half * (TILE_SIGS / 2);
             mbar_wait(&tmem_full_bar, t & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
@@ -229,6 +262,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (cs > 1) cluster_sync_all();       // no CTA leaves while a peer can still write its shared memory or barriers
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -274,6 +308,8 @@ CUtensorMap make_map(const float* base, int inner, int outer, int box_rows)
 
 struct TcPlan {
     CUtensorMap a_hi, a_lo, p_hi, p_lo, p_hi_thin, p_lo_thin;
+    CUtensorMap p_hi_part[3], p_lo_part[3];   // 1/2 and 1/4 of the signal tile per box: cluster multicast (index = log2 cluster size)
+    int cluster;
     int n_pad, mp, rows_alloc, sms;
 };
 
@@ -289,9 +325,17 @@ TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp
         p->p_hi = make_map(P_hi, mp, rows_alloc, TILE_SIGS);
         p->p_lo = make_map(P_lo, mp, rows_alloc, TILE_SIGS);
         p->p_hi_thin = make_map(P_hi, mp, rows_alloc, THIN_SIGS);
+        for (int l = 1; l <= 2; ++l) {
+            p->p_hi_part[l] = make_map(P_hi, mp, rows_alloc, TILE_SIGS >> l);
+            p->p_lo_part[l] = make_map(P_lo, mp, rows_alloc, TILE_SIGS >> l);
+        }
         p->p_lo_thin = make_map(P_lo, mp, rows_alloc, THIN_SIGS);
     } catch (...) { delete p; throw; }
     p->n_pad = n_pad; p->mp = mp; p->rows_alloc = rows_alloc;
+    p->cluster = 2;
+    if (const char* e = getenv("SSB200_CLUSTER")) p->cluster = atoi(e);                              // tuning knob: 1, 2 or 4
+    if (p->cluster != 1 && p->cluster != 2 && p->cluster != 4) p->cluster = 1;
+    while (p->cluster > 1 && (n_pad / TILE_ATOMS) % p->cluster != 0) p->cluster >>= 1;
     int dev = 0;
     SSB_CUDA(cudaGetDevice(&dev));
     SSB_CUDA(cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, dev));
@@ -309,10 +353,20 @@ void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
     const bool thin = rows <= THIN_SIGS;
     const int tile_sigs = thin ? THIN_SIGS : TILE_SIGS;
     const int sig_tiles = (rows + tile_sigs - 1) / tile_sigs;
-    const int grid = std::min(atom_tiles * sig_tiles, p->sms);
-    contract_tf32x3_kernel<<<grid, THREADS, SMEM_BYTES, stream>>>(p->a_hi, p->a_lo, thin ? p->p_hi_thin : p->p_hi,
-                                                                  thin ? p->p_lo_thin : p->p_lo, Q, ldq, rows,
-                                                                  atom_tiles, sig_tiles, p->mp / BLOCK_K, tile_sigs);
+    const int cs = thin ? 1 : p->cluster, lg = cs == 4 ? 2 : cs == 2 ? 1 : 0;
+    const int items = (atom_tiles / cs) * sig_tiles;
+    const int grid = std::min(items, p->sms / cs) * cs;
+    const CUtensorMap& mh = thin ? p->p_hi_thin : lg ? p->p_hi_part[lg] : p->p_hi;
+    const CUtensorMap& ml = thin ? p->p_lo_thin : lg ? p->p_lo_part[lg] : p->p_lo;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    const int k_blocks = p->mp / BLOCK_K;
+    SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_tf32x3_kernel, p->a_hi, p->a_lo, mh, ml, Q, ldq, rows, atom_tiles, sig_tiles,
+                                k_blocks, tile_sigs));
     SSB_CUDA(cudaGetLastError());
 }
 

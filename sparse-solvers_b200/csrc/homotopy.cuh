@@ -177,7 +177,7 @@ private:
         return (size_t)(2 * Npad + 4 * Mp + (size_t)kmax * kmax + 2 * kmax + 4) * sizeof(T) + 6 * sizeof(int);
     }
     // signals per chunk and number of lanes for a batch
-    void plan_batch(size_t batch, int kmax, size_t& chunk, int& nlanes);
+    void plan_batch(size_t batch, int kmax, bool host_path, size_t& chunk, int& nlanes);
     void reserve_workspace(Lane& L, size_t rows, int kmax);
     bool use_tc(size_t rows) const {
         if (sizeof(T) != 4) return false;
