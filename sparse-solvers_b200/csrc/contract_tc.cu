@@ -101,6 +101,37 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 __device__ __forceinline__ uint32_t cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ uint32_t cluster_size() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+
+// ---- CTA-pair (cta_group::2) variants: one UMMA spans two SMs, M = 256 atoms, each SM feeds its own 128 atom rows and
+// HALF of the signal rows from its own shared memory -- the operand bytes each SM moves per MAC drop by a third.
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* leader_bar, int c0, int c1) {
+    // executed by both CTAs; clearing the peer bit makes the transaction bytes land on CTA 0's barrier
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(leader_bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {   // arrives on `bar` in both CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta0(uint64_t* bar) {    // arrive on CTA 0's copy of `bar`
+    asm volatile(
+        "{\n"
+        ".reg .b32 ra;\n"
+        "mapa.shared::cluster.u32 ra, %0, 0;\n"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+        "}\n" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -269,6 +300,139 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
     }
 }
 
+// ---- CTA-pair kernel: the tile is 256 atoms x 256 signals over two SMs (cluster of 2, same TPC).  CTA r owns atom rows
+// [128 r, 128 r + 128) of the tile (operand A and the matching 128 TMEM lanes) and signal rows [128 r, 128 r + 128) of
+// the P tile (its half of operand B).  Both CTAs run a TMA producer whose bytes land on CTA 0's full barrier; CTA 0
+// alone issues tcgen05.mma.cta_group::2; its commits arrive on both CTAs' empty / tmem_full barriers; both CTAs'
+// epilogue warps drain their own TMEM half and arrive on CTA 0's tmem_empty barrier.
+constexpr int PAIR_HALF_SIGS = TILE_SIGS / 2;
+constexpr int PAIR_P_BYTES = PAIR_HALF_SIGS * ROW_BYTES;                  // 8 KB
+constexpr int PAIR_STAGE_BYTES = 2 * A_TILE_BYTES + 2 * PAIR_P_BYTES;     // 32 KB per CTA
+constexpr int PAIR_STAGES = 6;
+constexpr int PAIR_SMEM_BYTES = PAIR_STAGES * PAIR_STAGE_BYTES + 1024;
+
+__global__ void __launch_bounds__(THREADS, 1)
+contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                            const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
+                            float* __restrict__ Q, int ldq, int rows, int atom_pairs, int sig_tiles, int k_blocks)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], tmem_full_bar, tmem_empty_bar;
+    __shared__ uint32_t tmem_base_slot;
+
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int crank = (int)cluster_rank();
+    const int num_items = atom_pairs * sig_tiles;
+    const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < PAIR_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&tmem_full_bar, 1);
+        mbar_init(&tmem_empty_bar, 2 * EPI_WARPS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int item = pair_id; item < num_items; item += num_pairs) {
+                const int n0 = ((item % atom_pairs) * 2 + crank) * TILE_ATOMS;
+                const int r0 = (item / atom_pairs) * TILE_SIGS + crank * PAIR_HALF_SIGS;
+                for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+                    const int s = it % PAIR_STAGES;
+                    mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) & 1) ^ 1);
+                    uint8_t* st = smem + (size_t)s * PAIR_STAGE_BYTES;
+                    if (crank == 0) mbar_expect_tx(&full_bar[s], 2 * PAIR_STAGE_BYTES);   // both CTAs' bytes
+                    tma_load_2d_pair(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
+                    tma_load_2d_pair(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
+                    tma_load_2d_pair(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
+                    tma_load_2d_pair(st + 2 * A_TILE_BYTES + PAIR_P_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (CTA 0 only) =====
+        if (lane == 0 && crank == 0) {
+            uint32_t it = 0, t = 0;
+            const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
+            // D = F32, A = B = TF32, K-major, M = 256 (over the pair), N = 256
+            const uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TILE_SIGS >> 3) << 17) | ((uint32_t)((2 * TILE_ATOMS) >> 4) << 24);
+            for (int item = pair_id; item < num_items; item += num_pairs, ++t) {
+                mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+                    const int s = it % PAIR_STAGES;
+                    mbar_wait(&full_bar[s], (it / PAIR_STAGES) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    uint8_t* st = smem + (size_t)s * PAIR_STAGE_BYTES;
+                    const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + A_TILE_BYTES);
+                    const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + PAIR_P_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+                        const uint64_t adv = (uint64_t)((kk * UMMA_K * 4) >> 4);
+                        umma_tf32_pair(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                        umma_tf32_pair(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
+                        umma_tf32_pair(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                    }
+                    umma_commit_pair(&empty_bar[s]);
+                }
+                umma_commit_pair(&tmem_full_bar);
+            }
+        }
+    } else {
+        // ===== epilogue (both CTAs): own TMEM half -> registers -> Q =====
+        const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;
+        uint32_t t = 0;
+        for (int item = pair_id; item < num_items; item += num_pairs, ++t) {
+            const int n0 = ((item % atom_pairs) * 2 + crank) * TILE_ATOMS;
+            const int r0 = (item / atom_pairs) * TILE_SIGS + half * (TILE_SIGS / 2);
+            mbar_wait(&tmem_full_bar, t & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
+            float* qcol = Q + n0 + quarter * 32 + lane;
+            float r[TILE_SIGS / 2];
+#pragma unroll
+            for (int c0 = 0; c0 < TILE_SIGS / 2; c0 += 32) {
+                uint32_t v[32], w[32];
+                tmem_ld32(taddr0 + (uint32_t)c0, v);
+                tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[c0 + j] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cta0(&tmem_empty_bar);
+#pragma unroll
+            for (int j = 0; j < TILE_SIGS / 2; ++j) {
+                const int rr = r0 + j;
+                if (rr < rows) qcol[(size_t)rr * ldq] = r[j];
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    }
+}
+
 // ---- TMA descriptors through the driver entry point (no link-time libcuda dependency) -------------------
 using encode_fn_t = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -310,6 +474,7 @@ struct TcPlan {
     CUtensorMap a_hi, a_lo, p_hi, p_lo, p_hi_thin, p_lo_thin;
     CUtensorMap p_hi_part[3], p_lo_part[3];   // 1/2 and 1/4 of the signal tile per box: cluster multicast (index = log2 cluster size)
     int cluster;
+    bool pair;                                // CTA-pair (cta_group::2) kernel for full-width tiles
     int n_pad, mp, rows_alloc, sms;
 };
 
@@ -336,6 +501,9 @@ TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp
     if (const char* e = getenv("SSB200_CLUSTER")) p->cluster = atoi(e);                              // tuning knob: 1, 2 or 4
     if (p->cluster != 1 && p->cluster != 2 && p->cluster != 4) p->cluster = 1;
     while (p->cluster > 1 && (n_pad / TILE_ATOMS) % p->cluster != 0) p->cluster >>= 1;
+    p->pair = (n_pad / TILE_ATOMS) % 2 == 0;
+    if (const char* e = getenv("SSB200_PAIR")) p->pair = p->pair && atoi(e) != 0;                   // tuning knob
+    SSB_CUDA(cudaFuncSetAttribute(contract_tf32x3_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES));
     int dev = 0;
     SSB_CUDA(cudaGetDevice(&dev));
     SSB_CUDA(cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, dev));
@@ -353,6 +521,19 @@ void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
     const bool thin = rows <= THIN_SIGS;
     const int tile_sigs = thin ? THIN_SIGS : TILE_SIGS;
     const int sig_tiles = (rows + tile_sigs - 1) / tile_sigs;
+    if (!thin && p->pair) {
+        const int atom_pairs = atom_tiles / 2, items = atom_pairs * sig_tiles;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / 2) * 2)); cfg.blockDim = dim3(THREADS);
+        cfg.dynamicSmemBytes = PAIR_SMEM_BYTES; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_tf32x3_pair_kernel, p->a_hi, p->a_lo, p->p_hi_part[1], p->p_lo_part[1], Q, ldq,
+                                    rows, atom_pairs, sig_tiles, p->mp / BLOCK_K));
+        return;
+    }
     const int cs = thin ? 1 : p->cluster, lg = cs == 4 ? 2 : cs == 2 ? 1 : 0;
     const int items = (atom_tiles / cs) * sig_tiles;
     const int grid = std::min(items, p->sms / cs) * cs;
