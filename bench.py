@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=None, help="signals per GPU per step (default: the config's)")
-    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05", "tcgen05-tf32"])
     ap.add_argument("--cpu-sample", type=int, default=None, help="signals in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -264,6 +264,6 @@ int ssb200_set_timing(void* h, int enabled)
 int ssb200_get_timing(void* h, double ms[2])
 { return guarded([&] { SSB_REQUIRE(h && ms, "null pointer"); auto* b = static_cast<SolverBase*>(h); ms[0] = b->ms[0]; ms[1] = b->ms[1]; }); }
 int ssb200_set_contraction_path(void* h, int path)
-{ return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 2, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
+{ return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 3, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
 
 }  // extern "C"

@@ -132,6 +132,18 @@ __device__ __forceinline__ void mbar_arrive_cta0(uint64_t* bar) {    // arrive o
         "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
         "}\n" ::"r"(smem_u32(bar)) : "memory");
 }
+// one wrapper per (container type, CTA group): F16 = operands are fp16 (kind::f16), else tf32 containers (kind::tf32)
+template <bool F16, bool PAIR>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    if constexpr (F16 && PAIR)
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else if constexpr (F16)
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n"
+                     ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else if constexpr (PAIR) umma_tf32_pair(tmem_d, adesc, bdesc, idesc, accumulate);
+    else umma_tf32(tmem_d, adesc, bdesc, idesc, accumulate);
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -159,16 +171,21 @@ __device__ __forceinline__ uint64_t make_desc(const void* tile) {
 }
 
 // instruction descriptor: D = F32, A = B = TF32, both K-major, M = 128, N = 256
-__host__ __device__ constexpr uint32_t make_idesc(int n_sigs) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_sigs >> 3) << 17) | ((uint32_t)(TILE_ATOMS >> 4) << 24);
+// (a/b format: 0 = F16 under kind::f16, 2 = TF32 under kind::tf32)
+__host__ __device__ constexpr uint32_t make_idesc(int n_sigs, bool f16, int m_atoms = TILE_ATOMS) {
+    return (1u << 4) | ((f16 ? 0u : 2u) << 7) | ((f16 ? 0u : 2u) << 10) | ((uint32_t)(n_sigs >> 3) << 17) | ((uint32_t)(m_atoms >> 4) << 24);
 }
+constexpr float CORR_SCALE = 1.0f / 2048.0f;   // the fp16 lo parts are stored times 2^11
 constexpr int THIN_SIGS = 32;       // UMMA N of the thin-tail variant (same accumulation per element, 1/8 of the tensor and TMA work)
 
+template <bool F16>
 __global__ void __launch_bounds__(THREADS, 1)
-contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
-                       const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
-                       float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks, int tile_sigs)
+contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                   const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
+                   float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks, int tile_sigs,
+                   const float* __restrict__ a_inv, const float* __restrict__ p_inv)
 {
+    constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;     // operand elements per K-block
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
@@ -214,15 +231,15 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
                     mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);      // every CTA of the cluster has drained stage s
                     uint8_t* st = smem + (size_t)s * STAGE_BYTES;
                     mbar_expect_tx(&full_bar[s], 2 * A_TILE_BYTES + 2 * tile_sigs * ROW_BYTES);
-                    tma_load_2d(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
-                    tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
+                    tma_load_2d(st, &map_a_hi, &full_bar[s], kb * KB_ELEMS, n0);
+                    tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * KB_ELEMS, n0);
                     uint8_t* ph = st + 2 * A_TILE_BYTES + crank * part_bytes;
                     if (cs == 1) {
-                        tma_load_2d(ph, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
-                        tma_load_2d(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                        tma_load_2d(ph, &map_p_hi, &full_bar[s], kb * KB_ELEMS, r0);
+                        tma_load_2d(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0);
                     } else {
-                        tma_load_2d_mc(ph, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0 + crank * part_rows, cmask);
-                        tma_load_2d_mc(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0 + crank * part_rows, cmask);
+                        tma_load_2d_mc(ph, &map_p_hi, &full_bar[s], kb * KB_ELEMS, r0 + crank * part_rows, cmask);
+                        tma_load_2d_mc(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0 + crank * part_rows, cmask);
                     }
                 }
             }
@@ -232,7 +249,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
         if (lane == 0) {
             uint32_t it = 0, t = 0;
             const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
-            const uint32_t IDESC = make_idesc(tile_sigs);
+            const uint32_t IDESC = make_idesc(tile_sigs, F16);
             for (int item = cluster_id; item < num_items; item += num_clusters, ++t) {
                 mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -244,11 +261,11 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
                     const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + A_TILE_BYTES);
                     const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + P_TILE_BYTES);
 #pragma unroll
-                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
-                        const uint64_t adv = (uint64_t)((kk * UMMA_K * 4) >> 4);   // bytes along K inside the swizzle span
-                        umma_tf32(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
-                        umma_tf32(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
-                        umma_tf32(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                    for (int kk = 0; kk < ROW_BYTES / 32; ++kk) {                  // one UMMA K-step = 32 bytes of every row
+                        const uint64_t adv = (uint64_t)(kk * 2);                   // ... in 16-byte units inside the swizzle span
+                        umma<F16, false>(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                        umma<F16, false>(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
+                        umma<F16, false>(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
                     }
                     if (cs == 1) umma_commit(&empty_bar[s]);   // frees the smem stage when these MMAs retire
                     else umma_commit_mc(&empty_bar[s], cmask);  // ... in every CTA that multicasts into it
@@ -268,6 +285,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
             float* qcol = Q + n0 + quarter * 32 + lane;
+            const float ainv = F16 ? __ldg(a_inv + n0 + quarter * 32 + lane) : 1.0f;   // undoes the atom's power-of-two scale
             // drain both accumulators into registers first and hand TMEM back: the next tile's MMAs run while
             // this tile's stores are still in flight (with both accumulators resident TMEM cannot be double-buffered)
             float r[TILE_SIGS / 2];
@@ -278,7 +296,8 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
                 tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 32; ++j) r[c0 + j] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
+                for (int j = 0; j < 32; ++j)
+                    r[c0 + j] = F16 ? fmaf(__uint_as_float(w[j]), CORR_SCALE, __uint_as_float(v[j])) : __uint_as_float(v[j]) + __uint_as_float(w[j]);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
@@ -286,7 +305,7 @@ contract_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gri
 #pragma unroll
             for (int j = 0; j < TILE_SIGS / 2; ++j) {
                 const int rr = r0 + j;
-                if (rr < rows && half * (TILE_SIGS / 2) + j < tile_sigs) qcol[(size_t)rr * ldq] = r[j];
+                if (rr < rows && half * (TILE_SIGS / 2) + j < tile_sigs) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
             }
         }
     }
@@ -311,11 +330,14 @@ constexpr int PAIR_STAGE_BYTES = 2 * A_TILE_BYTES + 2 * PAIR_P_BYTES;     // 32 
 constexpr int PAIR_STAGES = 6;
 constexpr int PAIR_SMEM_BYTES = PAIR_STAGES * PAIR_STAGE_BYTES + 1024;
 
+template <bool F16>
 __global__ void __launch_bounds__(THREADS, 1)
-contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
-                            const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
-                            float* __restrict__ Q, int ldq, int rows, int atom_pairs, int sig_tiles, int k_blocks)
+contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                        const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
+                        float* __restrict__ Q, int ldq, int rows, int atom_pairs, int sig_tiles, int k_blocks,
+                        const float* __restrict__ a_inv, const float* __restrict__ p_inv)
 {
+    constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
@@ -355,10 +377,10 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
                     mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) & 1) ^ 1);
                     uint8_t* st = smem + (size_t)s * PAIR_STAGE_BYTES;
                     if (crank == 0) mbar_expect_tx(&full_bar[s], 2 * PAIR_STAGE_BYTES);   // both CTAs' bytes
-                    tma_load_2d_pair(st, &map_a_hi, &full_bar[s], kb * BLOCK_K, n0);
-                    tma_load_2d_pair(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * BLOCK_K, n0);
-                    tma_load_2d_pair(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * BLOCK_K, r0);
-                    tma_load_2d_pair(st + 2 * A_TILE_BYTES + PAIR_P_BYTES, &map_p_lo, &full_bar[s], kb * BLOCK_K, r0);
+                    tma_load_2d_pair(st, &map_a_hi, &full_bar[s], kb * KB_ELEMS, n0);
+                    tma_load_2d_pair(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * KB_ELEMS, n0);
+                    tma_load_2d_pair(st + 2 * A_TILE_BYTES, &map_p_hi, &full_bar[s], kb * KB_ELEMS, r0);
+                    tma_load_2d_pair(st + 2 * A_TILE_BYTES + PAIR_P_BYTES, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0);
                 }
             }
         }
@@ -367,8 +389,7 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
         if (lane == 0 && crank == 0) {
             uint32_t it = 0, t = 0;
             const uint32_t d_main = tmem_base, d_corr = tmem_base + TILE_SIGS;
-            // D = F32, A = B = TF32, K-major, M = 256 (over the pair), N = 256
-            const uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TILE_SIGS >> 3) << 17) | ((uint32_t)((2 * TILE_ATOMS) >> 4) << 24);
+            const uint32_t IDESC = make_idesc(TILE_SIGS, F16, 2 * TILE_ATOMS);   // M = 256 over the pair
             for (int item = pair_id; item < num_items; item += num_pairs, ++t) {
                 mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -380,11 +401,11 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
                     const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + A_TILE_BYTES);
                     const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + PAIR_P_BYTES);
 #pragma unroll
-                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
-                        const uint64_t adv = (uint64_t)((kk * UMMA_K * 4) >> 4);
-                        umma_tf32_pair(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
-                        umma_tf32_pair(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
-                        umma_tf32_pair(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                    for (int kk = 0; kk < ROW_BYTES / 32; ++kk) {
+                        const uint64_t adv = (uint64_t)(kk * 2);
+                        umma<F16, true>(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
+                        umma<F16, true>(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
+                        umma<F16, true>(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
                     }
                     umma_commit_pair(&empty_bar[s]);
                 }
@@ -403,6 +424,7 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
             float* qcol = Q + n0 + quarter * 32 + lane;
+            const float ainv = F16 ? __ldg(a_inv + n0 + quarter * 32 + lane) : 1.0f;   // undoes the atom's power-of-two scale
             float r[TILE_SIGS / 2];
 #pragma unroll
             for (int c0 = 0; c0 < TILE_SIGS / 2; c0 += 32) {
@@ -411,7 +433,8 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
                 tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 32; ++j) r[c0 + j] = __uint_as_float(v[j]) + __uint_as_float(w[j]);
+                for (int j = 0; j < 32; ++j)
+                    r[c0 + j] = F16 ? fmaf(__uint_as_float(w[j]), CORR_SCALE, __uint_as_float(v[j])) : __uint_as_float(v[j]) + __uint_as_float(w[j]);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
@@ -419,7 +442,7 @@ contract_tf32x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const 
 #pragma unroll
             for (int j = 0; j < TILE_SIGS / 2; ++j) {
                 const int rr = r0 + j;
-                if (rr < rows) qcol[(size_t)rr * ldq] = r[j];
+                if (rr < rows) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
             }
         }
     }
@@ -452,103 +475,119 @@ encode_fn_t get_encode()
     return fn;
 }
 
-CUtensorMap make_map(const float* base, int inner, int outer, int box_rows)
+CUtensorMap make_map(bool f16, const void* base, int inner, int outer, int box_rows)
 {
     encode_fn_t enc = get_encode();
     if (!enc) throw invalid_argument{ "cuTensorMapEncodeTiled is not available from this driver" };
     CUtensorMap m;
+    const size_t esz = f16 ? 2 : 4;
     cuuint64_t dims[2] = { (cuuint64_t)inner, (cuuint64_t)outer };
-    cuuint64_t strides[1] = { (cuuint64_t)inner * sizeof(float) };
-    cuuint32_t box[2] = { (cuuint32_t)BLOCK_K, (cuuint32_t)box_rows };
+    cuuint64_t strides[1] = { (cuuint64_t)inner * esz };
+    cuuint32_t box[2] = { (cuuint32_t)(ROW_BYTES / esz), (cuuint32_t)box_rows };
     cuuint32_t estr[2] = { 1, 1 };
-    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, ROW_BYTES == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+    CUresult r = enc(&m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
+                     strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     ROW_BYTES == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) throw invalid_argument{ "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")" };
     return m;
 }
 
+template <bool F16>
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream);
+
 }  // namespace
 
 struct TcPlan {
+    bool f16;                                 // operand containers: fp16 with power-of-two row scales, or tf32
     CUtensorMap a_hi, a_lo, p_hi, p_lo, p_hi_thin, p_lo_thin;
-    CUtensorMap p_hi_part[3], p_lo_part[3];   // 1/2 and 1/4 of the signal tile per box: cluster multicast (index = log2 cluster size)
-    int cluster;
+    CUtensorMap p_hi_part[3], p_lo_part[3];   // 1/2 and 1/4 of the signal tile per box (index = log2 cluster size)
+    const float* a_inv; const float* p_inv;   // fp16 containers: 1 / scale of every atom row and every signal row
+    int cluster;                              // single-CTA kernel: CTAs that share one multicast P tile
     bool pair;                                // CTA-pair (cta_group::2) kernel for full-width tiles
     int n_pad, mp, rows_alloc, sms;
 };
 
-bool tc_supported(int n_pad, int mp) { return n_pad % TILE_ATOMS == 0 && mp % BLOCK_K == 0 && get_encode() != nullptr; }
+bool tc_supported(int n_pad, int mp) { return n_pad % TILE_ATOMS == 0 && mp % 32 == 0 && get_encode() != nullptr; }
 
-TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp, const float* P_hi, const float* P_lo, int rows_alloc)
+TcPlan* tc_plan_create(bool f16, const void* At_hi, const void* At_lo, int n_pad, int mp, const void* P_hi, const void* P_lo,
+                       int rows_alloc, const float* a_inv, const float* p_inv)
 {
     SSB_REQUIRE(rows_alloc % TILE_SIGS == 0, "P buffers must be allocated in multiples of 256 rows");
     auto* p = new TcPlan;
     try {
-        p->a_hi = make_map(At_hi, mp, n_pad, TILE_ATOMS);
-        p->a_lo = make_map(At_lo, mp, n_pad, TILE_ATOMS);
-        p->p_hi = make_map(P_hi, mp, rows_alloc, TILE_SIGS);
-        p->p_lo = make_map(P_lo, mp, rows_alloc, TILE_SIGS);
-        p->p_hi_thin = make_map(P_hi, mp, rows_alloc, THIN_SIGS);
+        p->a_hi = make_map(f16, At_hi, mp, n_pad, TILE_ATOMS);
+        p->a_lo = make_map(f16, At_lo, mp, n_pad, TILE_ATOMS);
+        p->p_hi = make_map(f16, P_hi, mp, rows_alloc, TILE_SIGS);
+        p->p_lo = make_map(f16, P_lo, mp, rows_alloc, TILE_SIGS);
+        p->p_hi_thin = make_map(f16, P_hi, mp, rows_alloc, THIN_SIGS);
+        p->p_lo_thin = make_map(f16, P_lo, mp, rows_alloc, THIN_SIGS);
         for (int l = 1; l <= 2; ++l) {
-            p->p_hi_part[l] = make_map(P_hi, mp, rows_alloc, TILE_SIGS >> l);
-            p->p_lo_part[l] = make_map(P_lo, mp, rows_alloc, TILE_SIGS >> l);
+            p->p_hi_part[l] = make_map(f16, P_hi, mp, rows_alloc, TILE_SIGS >> l);
+            p->p_lo_part[l] = make_map(f16, P_lo, mp, rows_alloc, TILE_SIGS >> l);
         }
-        p->p_lo_thin = make_map(P_lo, mp, rows_alloc, THIN_SIGS);
     } catch (...) { delete p; throw; }
+    p->f16 = f16; p->a_inv = a_inv; p->p_inv = p_inv;
     p->n_pad = n_pad; p->mp = mp; p->rows_alloc = rows_alloc;
-    p->cluster = 2;
+    p->cluster = 1;
     if (const char* e = getenv("SSB200_CLUSTER")) p->cluster = atoi(e);                              // tuning knob: 1, 2 or 4
     if (p->cluster != 1 && p->cluster != 2 && p->cluster != 4) p->cluster = 1;
     while (p->cluster > 1 && (n_pad / TILE_ATOMS) % p->cluster != 0) p->cluster >>= 1;
     p->pair = (n_pad / TILE_ATOMS) % 2 == 0;
     if (const char* e = getenv("SSB200_PAIR")) p->pair = p->pair && atoi(e) != 0;                   // tuning knob
-    SSB_CUDA(cudaFuncSetAttribute(contract_tf32x3_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES));
     int dev = 0;
     SSB_CUDA(cudaGetDevice(&dev));
     SSB_CUDA(cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, dev));
-    SSB_CUDA(cudaFuncSetAttribute(contract_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    SSB_CUDA(cudaFuncSetAttribute(contract_x3_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES));
+    SSB_CUDA(cudaFuncSetAttribute(contract_x3_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES));
+    SSB_CUDA(cudaFuncSetAttribute(contract_x3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    SSB_CUDA(cudaFuncSetAttribute(contract_x3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     return p;
 }
 
 void tc_plan_destroy(TcPlan* p) { delete p; }
 
-void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
+namespace {
+template <bool F16>
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
 {
-    if (rows <= 0) return;
-    SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
     const int atom_tiles = p->n_pad / TILE_ATOMS;
     const bool thin = rows <= THIN_SIGS;
     const int tile_sigs = thin ? THIN_SIGS : TILE_SIGS;
     const int sig_tiles = (rows + tile_sigs - 1) / tile_sigs;
+    const int k_blocks = p->mp / (F16 ? ROW_BYTES / 2 : ROW_BYTES / 4);
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cfg.blockDim = dim3(THREADS); cfg.stream = stream;
     if (!thin && p->pair) {
         const int atom_pairs = atom_tiles / 2, items = atom_pairs * sig_tiles;
-        cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / 2) * 2)); cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = PAIR_SMEM_BYTES; cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-        SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_tf32x3_pair_kernel, p->a_hi, p->a_lo, p->p_hi_part[1], p->p_lo_part[1], Q, ldq,
-                                    rows, atom_pairs, sig_tiles, p->mp / BLOCK_K));
+        cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / 2) * 2));
+        cfg.dynamicSmemBytes = PAIR_SMEM_BYTES;
+        attr[0].val.clusterDim.x = 2;
+        SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_pair_kernel<F16>, p->a_hi, p->a_lo, p->p_hi_part[1], p->p_lo_part[1], Q, ldq,
+                                    rows, atom_pairs, sig_tiles, k_blocks, p->a_inv, p->p_inv));
         return;
     }
     const int cs = thin ? 1 : p->cluster, lg = cs == 4 ? 2 : cs == 2 ? 1 : 0;
     const int items = (atom_tiles / cs) * sig_tiles;
-    const int grid = std::min(items, p->sms / cs) * cs;
     const CUtensorMap& mh = thin ? p->p_hi_thin : lg ? p->p_hi_part[lg] : p->p_hi;
     const CUtensorMap& ml = thin ? p->p_lo_thin : lg ? p->p_lo_part[lg] : p->p_lo;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = SMEM_BYTES; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    const int k_blocks = p->mp / BLOCK_K;
-    SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_tf32x3_kernel, p->a_hi, p->a_lo, mh, ml, Q, ldq, rows, atom_tiles, sig_tiles,
-                                k_blocks, tile_sigs));
-    SSB_CUDA(cudaGetLastError());
+    cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / cs) * cs));
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    attr[0].val.clusterDim.x = (unsigned)cs;
+    SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_kernel<F16>, p->a_hi, p->a_lo, mh, ml, Q, ldq, rows, atom_tiles, sig_tiles,
+                                k_blocks, tile_sigs, p->a_inv, p->p_inv));
+}
+}  // namespace
+
+void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
+{
+    if (rows <= 0) return;
+    SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
+    if (p->f16) launch<true>(p, rows, Q, ldq, stream); else launch<false>(p, rows, Q, ldq, stream);
 }
 
 }  // namespace ssb

@@ -41,6 +41,30 @@ __global__ void tf32_split_kernel(const float* __restrict__ src, float* __restri
     }
 }
 
+// fp16 containers of the dictionary: every atom row times its own power of two, hi = fp16(a s), lo = fp16((a s - hi) 2^11);
+// a_inv[n] = 1 / s_n undoes the scale in the contraction epilogue; amax_bits collects max |A| (positive floats order as
+// unsigned integers).  One warp per atom.
+__global__ void f16_split_kernel(const float* __restrict__ src, __half* __restrict__ hi, __half* __restrict__ lo,
+                                 float* __restrict__ a_inv, unsigned int* __restrict__ amax_bits, int n_rows, int mp)
+{
+    const int lane = threadIdx.x & 31;
+    for (int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); n < n_rows; n += gridDim.x * (blockDim.x >> 5)) {
+        const float* row = src + (size_t)n * mp;
+        float mx = 0.f;
+        for (int m = lane; m < mp; m += 32) mx = fmaxf(mx, fabsf(row[m]));
+        mx = warp_max(mx);
+        const int e = f16_scale_exp(mx);
+        const float sc = ldexpf(1.f, e);
+        if (lane == 0) { a_inv[n] = ldexpf(1.f, -e); if (mx < FLT_MAX) atomicMax(amax_bits, __float_as_uint(mx)); }
+        for (int m = lane; m < mp; m += 32) {
+            const float v = row[m] * sc;
+            const __half h = __float2half_rn(v);
+            hi[(size_t)n * mp + m] = h;
+            lo[(size_t)n * mp + m] = __float2half_rn((v - __half2float(h)) * 2048.0f);
+        }
+    }
+}
+
 // Y[b][m] = sum_n A[m][n] X[b][n]   (ss::reconstruct_signal, src/lib.cpp:78-104), one CTA per signal
 template <typename T>
 __global__ void __launch_bounds__(128)
@@ -109,10 +133,11 @@ private:
     // path, its H2D / D2H copies).
     struct Lane {
         cudaStream_t stream = nullptr;
-        dev_buffer C, Q, P[2], Plo[2], gam, dG, Ginv, lam, K, pick, act[2], counts;
+        dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, act[2], counts;
         dev_buffer stY, stX, stIt, stErr;     // staging for the host-pointer entry points
         pinned_buffer h_count;
         TcPlan* plan[2] = { nullptr, nullptr };
+        bool plan_f16 = false;            // container flavour the plans were built for
         size_t ws_rows = 0;
         int ws_kmax = 0;
         // instrumentation, merged into the handle after the solve
@@ -145,6 +170,8 @@ private:
 
     dev_buffer dict_;                 // At | At_hi | At_lo | G in one slab (one L2 persistence window covers it)
     T* At_ = nullptr; T* At_hi_ = nullptr; T* At_lo_ = nullptr; T* G_ = nullptr;
+    __half* At16_hi_ = nullptr; __half* At16_lo_ = nullptr; float* a_inv_ = nullptr; unsigned int* amax_bits_ = nullptr;
+    float amax_ = 0.f;
     std::vector<std::unique_ptr<Lane>> lanes_;
     std::mutex merge_mu_;
     size_t l2_set_aside_ = 0;
@@ -159,12 +186,20 @@ private:
     }
     void alloc_dictionary() {
         const size_t a = (size_t)Npad * Mp, g = (size_t)Npad * Npad;
-        const size_t parts = sizeof(T) == 4 ? 3 : 1;
-        dict_.reserve((parts * a + g) * sizeof(T));
+        // float32: At | tf32 hi | tf32 lo | fp16 (hi, lo) | G | a_inv | amax ; float64: At | G
+        const size_t parts = sizeof(T) == 4 ? 4 : 1;
+        const size_t extra = sizeof(T) == 4 ? (size_t)Npad + 4 : 0;
+        dict_.reserve((parts * a + g + extra) * sizeof(T));
         At_ = dict_.as<T>();
         At_hi_ = sizeof(T) == 4 ? At_ + a : nullptr;
         At_lo_ = sizeof(T) == 4 ? At_ + 2 * a : nullptr;
         G_ = At_ + parts * a;
+        if (sizeof(T) == 4) {
+            At16_hi_ = reinterpret_cast<__half*>(At_ + 3 * a);
+            At16_lo_ = At16_hi_ + a;
+            a_inv_ = reinterpret_cast<float*>(G_ + g);
+            amax_bits_ = reinterpret_cast<unsigned int*>(a_inv_ + Npad);
+        }
     }
     void finish_dictionary();
     Lane& lane(int i) {
@@ -183,8 +218,14 @@ private:
         if (sizeof(T) != 4) return false;
         if (contraction_path == 1) return false;
         if (!tc_supported(Npad, Mp)) return false;
-        if (contraction_path == 2) return true;
+        if (contraction_path >= 2) return true;
         return rows >= 64;   // below that the tiles are mostly padding and the SIMT kernels win
+    }
+    // tensor-path containers: fp16 with power-of-two row scales (default), tf32 on request (path 3 / SSB200_TF32=1)
+    bool use_f16() const {
+        if (contraction_path == 3) return false;
+        if (const char* e = getenv("SSB200_TF32")) if (atoi(e) != 0) return false;   // tuning knob
+        return true;
     }
     void contract(Lane& L, bool tc, int which, size_t rows);
     void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,

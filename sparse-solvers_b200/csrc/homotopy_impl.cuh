@@ -13,7 +13,11 @@ void Homotopy<T>::finish_dictionary()
     if constexpr (sizeof(T) == 4) {
         tf32_split_kernel<<<1024, 256, 0, stream>>>(At_, At_hi_, At_lo_, (size_t)Npad * Mp);
         SSB_CUDA(cudaGetLastError());
-        counters[0]++;
+        SSB_CUDA(cudaMemsetAsync(amax_bits_, 0, sizeof(unsigned int), stream));
+        f16_split_kernel<<<(Npad + 7) / 8, 256, 0, stream>>>(reinterpret_cast<const float*>(At_), At16_hi_, At16_lo_, a_inv_, amax_bits_, Npad, Mp);
+        SSB_CUDA(cudaGetLastError());
+        SSB_CUDA(cudaMemcpyAsync(&amax_, amax_bits_, sizeof(float), cudaMemcpyDeviceToHost, stream));
+        counters[0] += 2;
     }
     SSB_CUDA(cudaStreamSynchronize(stream));
     for (auto& l : lanes_) l->drop_plans();
@@ -89,6 +93,7 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
             if (grew_lo) SSB_CUDA(cudaMemsetAsync(L.Plo[i].p, 0, L.Plo[i].bytes, L.stream));
         }
         L.act[i].reserve(r * sizeof(int));
+        L.Pinv[i].reserve(r * sizeof(float));
     }
     L.gam.reserve(r * k * sizeof(uint32_t));
     L.dG.reserve(r * k * sizeof(T));
@@ -111,9 +116,18 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows)
     const int span = L.begin(timing, 0);
     if constexpr (sizeof(T) == 4) {
         if (tc) {
-            if (!L.plan[which])
-                L.plan[which] = tc_plan_create(At_hi_, At_lo_, Npad, Mp, L.P[which].template as<float>(),
-                                               L.Plo[which].template as<float>(), (int)L.ws_rows);
+            const bool f16 = use_f16();
+            if (L.plan_f16 != f16) { L.drop_plans(); L.plan_f16 = f16; }
+            if (!L.plan[which]) {
+                if (f16) {
+                    __half* hi = L.Plo[which].template as<__half>();
+                    L.plan[which] = tc_plan_create(true, At16_hi_, At16_lo_, Npad, Mp, hi, hi + L.ws_rows * Mp, (int)L.ws_rows,
+                                                   a_inv_, L.Pinv[which].template as<float>());
+                } else {
+                    L.plan[which] = tc_plan_create(false, At_hi_, At_lo_, Npad, Mp, L.P[which].p, L.Plo[which].p, (int)L.ws_rows,
+                                                   nullptr, nullptr);
+                }
+            }
             tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream);
             L.counters[0]++;
         }
@@ -202,22 +216,37 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     a.gam = L.gam.template as<uint32_t>(); a.dG = L.dG.template as<T>(); a.Ginv = L.Ginv.template as<T>();
     a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>(); a.pick = L.pick.template as<uint32_t>();
     a.iters = d_iters; a.errs = d_errs;
-    a.split = tc ? 1 : 0;
+    const int tc_split = tc ? (use_f16() ? 2 : 1) : 0;
+    a.split = tc_split;
+    a.amax = amax_;
+    // where right-hand sides number i go for the current split (hi / full, lo, inverse scales)
+    auto set_rhs = [&](int i, int split) {
+        if (split == 2) {
+            __half* hi = L.Plo[i].template as<__half>();
+            a.Pn = reinterpret_cast<T*>(hi);
+            a.Pn_lo = reinterpret_cast<T*>(hi + L.ws_rows * Mp);
+            a.Pn_inv = L.Pinv[i].template as<float>();
+        } else {
+            a.Pn = L.P[i].template as<T>();
+            a.Pn_lo = split ? L.Plo[i].template as<T>() : nullptr;
+            a.Pn_inv = nullptr;
+        }
+    };
     a.tol = tol; a.max_iter = max_iter;
     if (const char* e = getenv("SSB200_DBG")) a.dbg = atoi(e);
 
     // c0 = A^T y for the whole chunk (homotopy-cpu.cpp:215)
     {
-        const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
-        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, L.P[0].template as<T>(),
-                                                       tc ? L.Plo[0].template as<T>() : nullptr, Mp, a.split);
+        set_rhs(0, a.split);
+        const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
+        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, a.Pn, a.Pn_lo, a.Pn_inv, Mp, a.split);
         SSB_CUDA(cudaGetLastError());
         L.counters[0]++;
     }
     contract(L, tc, 0, rows);
     {
         a.act = nullptr; a.act_next = nullptr; a.next_count = nullptr;
-        a.Pn = L.P[1].template as<T>(); a.Pn_lo = tc ? L.Plo[1].template as<T>() : nullptr;
+        set_rhs(1, a.split);
         a.it = 0;
         const int span = L.begin(timing, 1);
         homotopy_init_kernel<T, STEP_THREADS><<<(unsigned)rows, STEP_THREADS, 0, st>>>(a);
@@ -246,14 +275,13 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     for (uint32_t it = 1; it <= max_iter && count > 0; ++it) {
         contract(L, tc_cur, cur, count);
         const bool tc_next = tc_cur;   // (a SIMT tail would make a signal's rounding depend on the batch it travels in)
-        a.split = tc_next ? 1 : 0;
+        a.split = tc_next ? tc_split : 0;
         int* next_count = d_counts + (it & 1);
         SSB_CUDA(cudaMemsetAsync(next_count, 0, sizeof(int), st));
         a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
         a.act_next = L.act[cur ^ 1].template as<int>();
         a.next_count = next_count;
-        a.Pn = L.P[cur ^ 1].template as<T>();
-        a.Pn_lo = tc_next ? L.Plo[cur ^ 1].template as<T>() : nullptr;
+        set_rhs(cur ^ 1, a.split);
         a.it = it;
         const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
         const int ks = (kb + 1) | 1;                                          // odd row stride: conflict-free column reads
@@ -393,14 +421,21 @@ double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int 
     SSB_REQUIRE(M > 0 && rows > 0 && reps > 0, "bad arguments");
     Lane& L = lane(0);
     reserve_workspace(L, rows, 2);
-    const bool tc = path == 2;
+    const bool tc = path >= 2;
     SSB_REQUIRE(!tc || (sizeof(T) == 4 && tc_supported(Npad, Mp)), "tcgen05 contraction unavailable for this dtype/shape");
+    struct restore { int& ref; int v; ~restore() { ref = v; } } guard{ contraction_path, contraction_path };
+    contraction_path = path;                                 // 2: fp16 containers, 3: tf32 containers
+    const int split = tc ? (use_f16() ? 2 : 1) : 0;
     dev_buffer dP;
     dP.reserve(rows * M * sizeof(T));
     SSB_CUDA(cudaMemcpyAsync(dP.p, P, rows * M * sizeof(T), cudaMemcpyHostToDevice, L.stream));
-    const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
-    stage_signals_kernel<T><<<blocks, 256, 0, L.stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, L.P[0].template as<T>(),
-                                                         tc ? L.Plo[0].template as<T>() : nullptr, Mp, tc ? 1 : 0);
+    {
+        void* hi = split == 2 ? L.Plo[0].p : L.P[0].p;
+        void* lo = split == 2 ? static_cast<void*>(L.Plo[0].template as<__half>() + L.ws_rows * Mp) : split == 1 ? L.Plo[0].p : nullptr;
+        const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
+        stage_signals_kernel<T><<<blocks, 256, 0, L.stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, hi, lo,
+                                                             L.Pinv[0].template as<float>(), Mp, split);
+    }
     SSB_CUDA(cudaGetLastError());
     contract(L, tc, 0, rows);   // warm-up + the result
     cudaEvent_t e0 = L.event(), e1 = L.event();

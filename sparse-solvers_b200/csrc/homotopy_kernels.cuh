@@ -19,6 +19,8 @@
 //     summation order inside inv*u does.  A leaving atom's slot is refilled by the last slot.
 #pragma once
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace ssb {
@@ -49,8 +51,11 @@ struct HomArgs {
     int* next_count;
     uint32_t* pick;   // [Bc]        atom chosen by the min-gamma search (split kernels: scan -> algebra)
     T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
-    T* Pn_lo;         //             TF32 lo part (only when split != 0)
-    int split;
+    T* Pn_lo;         //             lo part (only when split != 0)
+    int split;        // how the right-hand sides are written: 0 full precision, 1 tf32 (hi, lo) floats, 2 fp16 (hi, lo * 2^11)
+                      // of the row times a power of two (Pn / Pn_lo then point at __half arrays, row stride ldp halfs)
+    float* Pn_inv;    // [rows]      split 2: 1 / scale of every right-hand side
+    float amax;       //             split 2: max |A|, bounds |p| <= amax * sum |d|
     T tol;
     uint32_t max_iter;
     uint32_t it;      // lockstep iteration number, 1-based
@@ -63,36 +68,80 @@ __device__ __forceinline__ float tf32_rna(float x) {
     return __uint_as_float(r);
 }
 
-// writes V consecutive values of p as full precision or as a TF32 hi/lo pair
+// Power-of-two scale that brings a row bounded by `bound` into the fp16 range: bound * 2^e <= 2^14.  A loose bound
+// only costs headroom: fp16 keeps 11 significant bits over 29 binades, so a bound 2^8 above the true maximum still leaves
+// every element within 2^-21 of it a normal number.
+__device__ __forceinline__ int f16_scale_exp(float bound) {
+    if (!(bound > 0.f) || !(bound < FLT_MAX)) return 0;
+    int ex;
+    frexpf(bound, &ex);                 // bound = m * 2^ex, m in [0.5, 1)
+    return max(-100, min(100, 14 - ex));
+}
+
+// writes V consecutive values of p: full precision, a TF32 (hi, lo) pair, or an fp16 (hi, lo * 2^11) pair of p * scale.
+// tf32 and fp16 both carry 11 significant bits, so the two splits have the same accuracy (hi + lo covers 22 bits);
+// the fp16 form feeds tcgen05.mma.kind::f16 at twice the tf32 rate and half the operand bytes.
 template <typename T, int V>
-__device__ __forceinline__ void store_rhs(T* hi, T* lo, int split, const T (&v)[V]) {
+__device__ __forceinline__ void store_rhs(int split, void* hi_row, void* lo_row, int m0, const T (&v)[V], float scale) {
     if constexpr (sizeof(T) == 4) {
-        if (split) {
+        if (split == 1) {
             float h[V], l[V];
 #pragma unroll
             for (int e = 0; e < V; ++e) { h[e] = tf32_rna(v[e]); l[e] = tf32_rna(v[e] - h[e]); }
-            *reinterpret_cast<int4*>(hi) = *reinterpret_cast<const int4*>(h);
-            *reinterpret_cast<int4*>(lo) = *reinterpret_cast<const int4*>(l);
+            *reinterpret_cast<int4*>(static_cast<float*>(hi_row) + m0) = *reinterpret_cast<const int4*>(h);
+            *reinterpret_cast<int4*>(static_cast<float*>(lo_row) + m0) = *reinterpret_cast<const int4*>(l);
+            return;
+        }
+        if (split == 2) {
+            __half h[V], l[V];
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const float ps = v[e] * scale;
+                h[e] = __float2half_rn(ps);
+                l[e] = __float2half_rn((ps - __half2float(h[e])) * 2048.0f);
+            }
+            *reinterpret_cast<uint2*>(static_cast<__half*>(hi_row) + m0) = *reinterpret_cast<const uint2*>(h);
+            *reinterpret_cast<uint2*>(static_cast<__half*>(lo_row) + m0) = *reinterpret_cast<const uint2*>(l);
             return;
         }
     }
-    *reinterpret_cast<int4*>(hi) = *reinterpret_cast<const int4*>(v);
+    *reinterpret_cast<int4*>(static_cast<T*>(hi_row) + m0) = *reinterpret_cast<const int4*>(v);
 }
 
-// Y (caller layout) -> first right-hand sides, zero padded to ldp
+// row `row` of the next right-hand sides, as bytes (the element size depends on the split)
+template <typename T>
+__device__ __forceinline__ void rhs_rows(const HomArgs<T>& a, int row, void*& hi, void*& lo) {
+    const size_t esz = a.split == 2 ? 2 : sizeof(T);
+    hi = reinterpret_cast<unsigned char*>(a.Pn) + (size_t)row * a.ldp * esz;
+    lo = a.split ? reinterpret_cast<unsigned char*>(a.Pn_lo) + (size_t)row * a.ldp * esz : nullptr;
+}
+
+// Y (caller layout) -> first right-hand sides, zero padded to ldp; one warp per signal (split 2 needs the row maximum)
 template <typename T>
 __global__ void stage_signals_kernel(const T* __restrict__ Y, size_t ldy, int M, int rows,
-                                     T* __restrict__ P, T* __restrict__ Plo, int ldp, int split)
+                                     void* __restrict__ P, void* __restrict__ Plo, float* __restrict__ Pinv, int ldp, int split)
 {
     constexpr int V = 16 / sizeof(T);
-    const size_t total = (size_t)rows * (ldp / V);
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        const size_t r = e / (ldp / V);
-        const int m0 = (int)(e % (ldp / V)) * V;
-        T v[V];
+    const int lane = threadIdx.x & 31;
+    const size_t esz = split == 2 ? 2 : sizeof(T);
+    for (size_t r = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < (size_t)rows; r += (size_t)gridDim.x * (blockDim.x >> 5)) {
+        float scale = 1.f;
+        if (split == 2) {
+            float mx = 0.f;
+            for (int m = lane; m < M; m += 32) mx = fmaxf(mx, fabsf((float)Y[r * ldy + m]));
+            mx = warp_max(mx);
+            const int e = f16_scale_exp(mx);
+            scale = ldexpf(1.f, e);
+            if (lane == 0) Pinv[r] = ldexpf(1.f, -e);
+        }
+        void* hi = static_cast<unsigned char*>(P) + r * ldp * esz;
+        void* lo = Plo ? static_cast<unsigned char*>(Plo) + r * ldp * esz : nullptr;
+        for (int m0 = lane * V; m0 < ldp; m0 += 32 * V) {
+            T v[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) v[k] = (m0 + k < M) ? Y[r * ldy + m0 + k] : T(0);
-        store_rhs<T, V>(P + r * ldp + m0, Plo ? Plo + r * ldp + m0 : nullptr, split, v);
+            for (int k = 0; k < V; ++k) v[k] = (m0 + k < M) ? Y[r * ldy + m0 + k] : T(0);
+            store_rhs<T, V>(split, hi, lo, m0, v, scale);
+        }
     }
 }
 
@@ -110,8 +159,16 @@ template <typename T, int THREADS>
 __device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, const uint32_t* s_gam, const T* s_d, int K)
 {
     constexpr int V = 16 / sizeof(T);
-    T* pn = a.Pn + (size_t)row * a.ldp;
-    T* pl = a.split ? a.Pn_lo + (size_t)row * a.ldp : nullptr;
+    void *pn, *pl;
+    rhs_rows(a, row, pn, pl);
+    float scale = 1.f;
+    if (a.split == 2) {   // |p_m| <= amax * sum |d_k|
+        float sd = 0.f;
+        for (int k = 0; k < K; ++k) sd += fabsf((float)s_d[k]);
+        const int e = f16_scale_exp(sd * a.amax);
+        scale = ldexpf(1.f, e);
+        if (threadIdx.x == 0) a.Pn_inv[row] = ldexpf(1.f, -e);
+    }
     for (int m0 = threadIdx.x * V; m0 < a.Mp; m0 += THREADS * V) {
         T acc[V];
 #pragma unroll
@@ -123,7 +180,7 @@ __device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, const ui
 #pragma unroll
             for (int e = 0; e < V; ++e) acc[e] += av[e] * dk;
         }
-        store_rhs<T, V>(pn + m0, pl ? pl + m0 : nullptr, a.split, acc);
+        store_rhs<T, V>(a.split, pn, pl, m0, acc, scale);
     }
 }
 

@@ -348,8 +348,17 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
     __syncwarp();
 
     // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs
-    T* pn = a.Pn + (size_t)row * a.ldp;
-    T* pl = a.split ? a.Pn_lo + (size_t)row * a.ldp : nullptr;
+    void *pn, *pl;
+    rhs_rows(a, row, pn, pl);
+    float scale = 1.f;
+    if (a.split == 2) {   // |p_m| <= amax * sum |d_k|
+        float sd = 0.f;
+        for (int k = lane; k < Knew; k += 32) sd += fabsf((float)s_d[k]);
+        sd = warp_sum(sd);
+        const int e = f16_scale_exp(sd * a.amax);
+        scale = ldexpf(1.f, e);
+        if (lane == 0) a.Pn_inv[row] = ldexpf(1.f, -e);
+    }
     for (int m0 = lane * V; m0 < a.Mp; m0 += 32 * V) {
         T acc[V];
 #pragma unroll
@@ -368,7 +377,7 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
                     for (int e = 0; e < V; ++e) acc[e] += av[u][e] * dk;
                 }
         }
-        store_rhs<T, V>(pn + m0, pl ? pl + m0 : nullptr, a.split, acc);
+        store_rhs<T, V>(a.split, pn, pl, m0, acc, scale);
     }
 }
 

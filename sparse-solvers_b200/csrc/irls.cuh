@@ -143,8 +143,8 @@ public:
         P_.reserve(round_up(chunk, 64) * Mp * sizeof(T));
         for (size_t b0 = 0; b0 < batch; b0 += chunk) {
             const size_t rows = std::min(chunk, batch - b0);
-            const int blocks = (int)std::min<size_t>(4096, (rows * (Mp / (16 / sizeof(T))) + 255) / 256);
-            stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY + b0 * ldy, ldy, M, (int)rows, P_.as<T>(), nullptr, Mp, 0);
+            const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
+            stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY + b0 * ldy, ldy, M, (int)rows, P_.as<T>(), nullptr, nullptr, Mp, 0);
             SSB_CUDA(cudaGetLastError());
             counters[0]++;
             // S = Q^T Y  (irls-cpu.cpp:53, the same for every iteration of a signal)

@@ -22,7 +22,7 @@ struct SolverBase {
     uint64_t counters[4] = { 0, 0, 0, 0 };
     bool timing = false;
     double ms[2] = { 0.0, 0.0 };
-    int contraction_path = 0;            // 0 auto, 1 SIMT, 2 tcgen05
+    int contraction_path = 0;            // 0 auto, 1 SIMT, 2 tcgen05 (fp16 containers), 3 tcgen05 with tf32 containers
 
     // pairs of events bracketing launches of class `cls` on the current solve's stream
     struct span { cudaEvent_t a, b; int cls; };
@@ -72,8 +72,10 @@ struct SolverBase {
 // At_hi/At_lo: [n_pad][mp], P_hi/P_lo: [rows_alloc][mp] with rows_alloc % 256 == 0 (rows beyond
 // `rows` are computed but not stored), Q: [rows][ldq].  n_pad % 128 == 0, mp % 32 == 0.
 struct TcPlan;   // holds the TMA descriptors of one (At, P, Q) buffer set
-TcPlan* tc_plan_create(const float* At_hi, const float* At_lo, int n_pad, int mp,
-                       const float* P_hi, const float* P_lo, int rows_alloc);
+// f16: operands are fp16 containers (hi, lo * 2^11) of rows scaled by powers of two, a_inv / p_inv undo the scales in the
+// epilogue; otherwise tf32 containers (float arrays) and no scales
+TcPlan* tc_plan_create(bool f16, const void* At_hi, const void* At_lo, int n_pad, int mp, const void* P_hi, const void* P_lo,
+                       int rows_alloc, const float* a_inv, const float* p_inv);
 void tc_plan_destroy(TcPlan*);
 void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream);
 bool tc_supported(int n_pad, int mp);

@@ -107,7 +107,7 @@ class _Solver:
         return dict(contraction_ms=ms[0], step_ms=ms[1])
 
     def set_contraction_path(self, path):
-        check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2}[path])))
+        check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path])))
 
 
 class Homotopy(_Solver):
@@ -157,7 +157,7 @@ class Homotopy(_Solver):
         Q = np.empty((P.shape[0], self.shape[1]), dtype=self.dtype)
         ms = C.c_double()
         check(getattr(lib(), f"ssb200_debug_contract_{self._sfx}")(
-            self._h, _ptr(P), C.c_size_t(P.shape[0]), _ptr(Q), C.c_int({"simt": 1, "tcgen05": 2}[path]), C.c_int(reps),
+            self._h, _ptr(P), C.c_size_t(P.shape[0]), _ptr(Q), C.c_int({"simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path]), C.c_int(reps),
             C.byref(ms)))
         return Q, ms.value
 

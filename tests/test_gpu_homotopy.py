@@ -26,7 +26,7 @@ def ss():
     return sparsesolvers
 
 
-@pytest.mark.parametrize("path", ["simt", "auto"])
+@pytest.mark.parametrize("path", ["simt", "auto", "tcgen05-tf32"])
 @pytest.mark.parametrize("name", HOMOTOPY_GOLDEN)
 def test_golden(ss, name, path):
     g = np.load(os.path.join(GOLDEN, name))
@@ -38,7 +38,7 @@ def test_golden(ss, name, path):
     check_homotopy(s, g["A"], g["Y"], float(g["tol"]), int(g["max_iter"]), g["X"], g["iters"], g["errs"], name)
 
 
-@pytest.mark.parametrize("path", ["simt", "auto"])
+@pytest.mark.parametrize("path", ["simt", "auto", "tcgen05-tf32"])
 @pytest.mark.parametrize("dtype,m,n,k,batch", [(np.float32, 128, 512, 10, 300), (np.float64, 128, 512, 10, 200),
                                                (np.float32, 256, 1024, 16, 256), (np.float32, 504, 1216, 20, 130),
                                                (np.float64, 100, 230, 7, 70)])
