@@ -287,14 +287,17 @@ def run_b200(args, cfg):
     flops = 2.0 * M * N * counters["contraction_rows"]
     achieved = flops / (timing["contraction_ms"] * 1e-3) / 1e12 if timing["contraction_ms"] > 0 else 0.0
     tensor_path = args.path != "simt" and dt == np.float32
-    # fp32-equivalent tensor peak of the 3xTF32 scheme: TF32 dense = bf16/2, three MMAs per product
-    peak = peaks["bf16_tflops_sustained"] / 6.0
+    # fp32-equivalent tensor peak of the three-product split: every fp32 product costs three tensor MMAs -- on fp16
+    # containers (default) at the bf16/fp16 rate, on tf32 containers (--path tcgen05-tf32) at half of it
+    tf32 = args.path == "tcgen05-tf32" or os.environ.get("SSB200_TF32", "0") not in ("", "0")
+    peak = peaks["bf16_tflops_sustained"] / (6.0 if tf32 else 3.0)
     roofline = {"kernel": "contract (Q = A^T P)", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                 "frac": achieved / peak, "traffic": None,
-                "peak_source": f"{peak_src} bf16_tflops_sustained / 6 (TF32 = bf16/2, 3 MMAs per fp32 product)",
+                "peak_source": f"{peak_src} bf16_tflops_sustained / " + ("6 (TF32 = bf16/2, 3 MMAs per fp32 product)" if tf32 else
+                               "3 (3 fp16-rate MMAs per fp32 product)"),
                 "launches": counters["contractions"], "avg_launch_ms": timing["contraction_ms"] / max(1, counters["contractions"]),
                 "share_of_step": timing["contraction_ms"] / ms, "step_kernel_share": timing["step_ms"] / ms,
-                "path": "tcgen05 3xTF32" if tensor_path else "simt fp32"}
+                "path": ("tcgen05 3-split, tf32 containers" if tf32 else "tcgen05 3-split, fp16 containers") if tensor_path else "simt fp32"}
     whole = {"achieved": 2.0 * M * N * world * batch * args.steps * (iters_mean + 1) / (ms * 1e-3) / 1e12,
              "unit": "TFLOP/s", "note": "whole-solve algorithmic flops 2*M*N*(iters+1) per signal / step time"}
     whole["frac"] = whole["achieved"] / (peak * world)

@@ -175,6 +175,7 @@ __device__ __forceinline__ uint64_t make_desc(const void* tile) {
 __host__ __device__ constexpr uint32_t make_idesc(int n_sigs, bool f16, int m_atoms = TILE_ATOMS) {
     return (1u << 4) | ((f16 ? 0u : 2u) << 7) | ((f16 ? 0u : 2u) << 10) | ((uint32_t)(n_sigs >> 3) << 17) | ((uint32_t)(m_atoms >> 4) << 24);
 }
+__device__ int g_tc_dbg = 0;   // timing experiments only (SSB200_TC_DBG): 1 no Q stores, 2 no MMA issue, 4 no TMEM drain
 constexpr float CORR_SCALE = 1.0f / 2048.0f;   // the fp16 lo parts are stored times 2^11
 constexpr int THIN_SIGS = 32;       // UMMA N of the thin-tail variant (same accumulation per element, 1/8 of the tensor and TMA work)
 
@@ -345,6 +346,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int crank = (int)cluster_rank();
+    const int dbg = g_tc_dbg;
     const int num_items = atom_pairs * sig_tiles;
     const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
 
@@ -403,6 +405,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
 #pragma unroll
                     for (int kk = 0; kk < ROW_BYTES / 32; ++kk) {
                         const uint64_t adv = (uint64_t)(kk * 2);
+                        if (dbg & 2) continue;
                         umma<F16, true>(d_corr, a_lo + adv, p_hi + adv, IDESC, (kb | kk) != 0);
                         umma<F16, true>(d_corr, a_hi + adv, p_lo + adv, IDESC, 1);
                         umma<F16, true>(d_main, a_hi + adv, p_hi + adv, IDESC, (kb | kk) != 0);
@@ -428,6 +431,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
             float r[TILE_SIGS / 2];
 #pragma unroll
             for (int c0 = 0; c0 < TILE_SIGS / 2; c0 += 32) {
+                if (dbg & 4) { for (int j = 0; j < 32; ++j) r[c0 + j] = 0.f; continue; }
                 uint32_t v[32], w[32];
                 tmem_ld32(taddr0 + (uint32_t)c0, v);
                 tmem_ld32(taddr0 + (uint32_t)(TILE_SIGS + c0), w);
@@ -442,7 +446,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
 #pragma unroll
             for (int j = 0; j < TILE_SIGS / 2; ++j) {
                 const int rr = r0 + j;
-                if (rr < rows) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
+                if (rr < rows && !(dbg & 1)) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
             }
         }
     }
@@ -528,6 +532,7 @@ TcPlan* tc_plan_create(bool f16, const void* At_hi, const void* At_lo, int n_pad
         }
     } catch (...) { delete p; throw; }
     p->f16 = f16; p->a_inv = a_inv; p->p_inv = p_inv;
+    { int dbg = 0; if (const char* e = getenv("SSB200_TC_DBG")) dbg = atoi(e); SSB_CUDA(cudaMemcpyToSymbol(g_tc_dbg, &dbg, sizeof(int))); }
     p->n_pad = n_pad; p->mp = mp; p->rows_alloc = rows_alloc;
     p->cluster = 1;
     if (const char* e = getenv("SSB200_CLUSTER")) p->cluster = atoi(e);                              // tuning knob: 1, 2 or 4

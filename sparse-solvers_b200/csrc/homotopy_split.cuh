@@ -11,10 +11,14 @@
 
 #include "homotopy_kernels.cuh"
 
+#ifndef SSB_SCAN_MINB
+#define SSB_SCAN_MINB 8   // resident scan CTAs of 128 threads per SM the register allocation aims for
+#endif
+
 namespace ssb {
 
 template <typename T, int THREADS, int NCH>
-__global__ void __launch_bounds__(THREADS) homotopy_scan_kernel(HomArgs<T> a)
+__global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a)
 {
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;

@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "csrc", "libssb200.so")
+LIB_PATH = os.environ.get("SSB200_LIB") or os.path.join(os.path.dirname(_HERE), "csrc", "libssb200.so")   # env: A/B builds
 _lib = None
 
 STATUS_OK = 0
