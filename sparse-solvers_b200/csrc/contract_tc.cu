@@ -184,9 +184,10 @@ __global__ void __launch_bounds__(THREADS, 1)
 contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                    const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
                    float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks, int tile_sigs,
-                   const float* __restrict__ a_inv, const float* __restrict__ p_inv)
+                   const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev)
 {
     constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;     // operand elements per K-block
+    if (rows_dev) { rows = min(rows, *rows_dev); sig_tiles = (rows + tile_sigs - 1) / tile_sigs; }   // host count may be stale (larger)
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
@@ -336,9 +337,10 @@ __global__ void __launch_bounds__(THREADS, 1)
 contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
                         float* __restrict__ Q, int ldq, int rows, int atom_pairs, int sig_tiles, int k_blocks,
-                        const float* __restrict__ a_inv, const float* __restrict__ p_inv)
+                        const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev)
 {
     constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;
+    if (rows_dev) { rows = min(rows, *rows_dev); sig_tiles = (rows + TILE_SIGS - 1) / TILE_SIGS; }
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
@@ -498,7 +500,7 @@ CUtensorMap make_map(bool f16, const void* base, int inner, int outer, int box_r
 }
 
 template <bool F16>
-void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream);
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev);
 
 }  // namespace
 
@@ -554,7 +556,7 @@ void tc_plan_destroy(TcPlan* p) { delete p; }
 
 namespace {
 template <bool F16>
-void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev)
 {
     const int atom_tiles = p->n_pad / TILE_ATOMS;
     const bool thin = rows <= THIN_SIGS;
@@ -573,7 +575,7 @@ void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
         cfg.dynamicSmemBytes = PAIR_SMEM_BYTES;
         attr[0].val.clusterDim.x = 2;
         SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_pair_kernel<F16>, p->a_hi, p->a_lo, p->p_hi_part[1], p->p_lo_part[1], Q, ldq,
-                                    rows, atom_pairs, sig_tiles, k_blocks, p->a_inv, p->p_inv));
+                                    rows, atom_pairs, sig_tiles, k_blocks, p->a_inv, p->p_inv, rows_dev));
         return;
     }
     const int cs = thin ? 1 : p->cluster, lg = cs == 4 ? 2 : cs == 2 ? 1 : 0;
@@ -584,15 +586,15 @@ void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
     cfg.dynamicSmemBytes = SMEM_BYTES;
     attr[0].val.clusterDim.x = (unsigned)cs;
     SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_kernel<F16>, p->a_hi, p->a_lo, mh, ml, Q, ldq, rows, atom_tiles, sig_tiles,
-                                k_blocks, tile_sigs, p->a_inv, p->p_inv));
+                                k_blocks, tile_sigs, p->a_inv, p->p_inv, rows_dev));
 }
 }  // namespace
 
-void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream)
+void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev)
 {
     if (rows <= 0) return;
     SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
-    if (p->f16) launch<true>(p, rows, Q, ldq, stream); else launch<false>(p, rows, Q, ldq, stream);
+    if (p->f16) launch<true>(p, rows, Q, ldq, stream, rows_dev); else launch<false>(p, rows, Q, ldq, stream, rows_dev);
 }
 
 }  // namespace ssb

@@ -145,10 +145,12 @@ private:
         struct span { cudaEvent_t a, b; int cls; };
         std::vector<span> spans;
         std::vector<cudaEvent_t> pool;
+        std::vector<cudaEvent_t> count_events;   // one per iteration in flight (count read-back)
         Lane() { SSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
         ~Lane() {
             drop_plans();
             for (auto e : pool) cudaEventDestroy(e);
+            for (auto e : count_events) cudaEventDestroy(e);
             for (auto& s : spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
             if (stream) cudaStreamDestroy(stream);
         }
@@ -227,7 +229,7 @@ private:
         if (const char* e = getenv("SSB200_TF32")) if (atoi(e) != 0) return false;   // tuning knob
         return true;
     }
-    void contract(Lane& L, bool tc, int which, size_t rows);
+    void contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev = nullptr, bool count_rows = false);
     void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                      uint32_t* d_iters, double* d_errs);
     void merge(Lane& L);

@@ -101,8 +101,8 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
     L.lam.reserve(r * sizeof(T));
     L.K.reserve(r * sizeof(int));
     L.pick.reserve(r * sizeof(uint32_t));
-    L.counts.reserve(2 * sizeof(int));
-    L.h_count.reserve(sizeof(int));
+    L.counts.reserve(4096 * sizeof(int));
+    L.h_count.reserve(4096 * sizeof(int));
     SSB_CUDA(cudaStreamSynchronize(L.stream));
     L.ws_rows = r;
     L.ws_kmax = k;
@@ -111,7 +111,7 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
 
 // Q[r][:] = A^T P[which][r][:] for r < rows
 template <typename T>
-void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows)
+void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev, bool count_rows)
 {
     const int span = L.begin(timing, 0);
     if constexpr (sizeof(T) == 4) {
@@ -128,7 +128,7 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows)
                                                    nullptr, nullptr);
                 }
             }
-            tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream);
+            tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream, rows_dev);
             L.counters[0]++;
         }
     }
@@ -137,7 +137,7 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows)
                                                  L.Q.template as<T>(), Npad, L.stream);
     L.end(span);
     L.counters[1]++;
-    L.counters[2] += rows;
+    if (count_rows) L.counters[2] += rows;
 }
 
 
@@ -243,7 +243,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_CUDA(cudaGetLastError());
         L.counters[0]++;
     }
-    contract(L, tc, 0, rows);
+    contract(L, tc, 0, rows, nullptr, true);
     {
         a.act = nullptr; a.act_next = nullptr; a.next_count = nullptr;
         set_rhs(1, a.split);
@@ -267,20 +267,40 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     bool split_ok = true;                                                                            // scan + algebra kernels
     if (const char* e = getenv("SSB200_SPLIT")) split_ok = atoi(e) != 0;                              // tuning knob
 
-    size_t count = rows;
+    // Lockstep loop.  The number of signals still running lives on the device: counts[it] is appended to by iteration
+    // it and read by iteration it + 1 (every kernel bounds itself by it), so the host never has to wait for an
+    // iteration before queueing the next.  It reads the counts back asynchronously, sizes the grids from the newest one
+    // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
+    // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
+    constexpr uint32_t RUN_AHEAD = 2;
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
-    int* d_counts = L.counts.template as<int>();
-    int* h_count = L.h_count.template as<int>();
-    bool tc_cur = tc;            // how P[cur] was written: TF32 hi/lo pair (tensor path) or full precision (SIMT path)
-    for (uint32_t it = 1; it <= max_iter && count > 0; ++it) {
-        contract(L, tc_cur, cur, count);
-        const bool tc_next = tc_cur;   // (a SIMT tail would make a signal's rounding depend on the batch it travels in)
-        a.split = tc_next ? tc_split : 0;
-        int* next_count = d_counts + (it & 1);
-        SSB_CUDA(cudaMemsetAsync(next_count, 0, sizeof(int), st));
+    int* d_counts = L.counts.template as<int>();        // [max_iter + 2]
+    int* h_counts = L.h_count.template as<int>();       // pinned mirror
+    SSB_CUDA(cudaMemsetAsync(d_counts, 0, ((size_t)max_iter + 2) * sizeof(int), st));
+    h_counts[0] = (int)rows;
+    SSB_CUDA(cudaMemcpyAsync(d_counts, h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+    while (L.count_events.size() < RUN_AHEAD + 1) { cudaEvent_t e; SSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); L.count_events.push_back(e); }
+    const bool async = tc;
+    size_t known = rows;         // newest count the host has seen (upper bound of the current one)
+    uint32_t seen = 0;           // ... which is counts[seen]
+    uint32_t last = 0;
+    for (uint32_t it = 1; it <= max_iter; ++it) {
+        const uint32_t must = async ? (it > RUN_AHEAD ? it - RUN_AHEAD : 0) : it - 1;   // counts[must] has to be in
+        for (uint32_t j = seen + 1; j < it; ++j) {
+            cudaEvent_t ev = L.count_events[j % (RUN_AHEAD + 1)];
+            if (j <= must) SSB_CUDA(cudaEventSynchronize(ev));
+            else if (cudaEventQuery(ev) != cudaSuccess) { cudaGetLastError(); break; }
+            seen = j;
+            known = (size_t)h_counts[j];
+        }
+        if (known == 0) break;
+        last = it;
+        contract(L, tc, cur, known, async ? d_counts + (it - 1) : nullptr);
+        a.split = tc ? tc_split : 0;
         a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
         a.act_next = L.act[cur ^ 1].template as<int>();
-        a.next_count = next_count;
+        a.count_in = d_counts + (it - 1);
+        a.next_count = d_counts + it;
         set_rhs(cur ^ 1, a.split);
         a.it = it;
         const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
@@ -290,25 +310,24 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
         SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
         const size_t slice = homotopy_algebra_slice<T>(kb, ks);
-        const int aw = (split_ok && count >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
+        const int aw = (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
         if (aw > 0) {
-            launch_scan(threads, nch, (unsigned)count, homotopy_scan_smem<T>(L.ws_kmax, Npad), st, a);
-            launch_algebra(aw, (unsigned)count, slice, st, a, kb, ks);
+            launch_scan(threads, nch, (unsigned)known, homotopy_scan_smem<T>(L.ws_kmax, Npad), st, a);
+            launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
             L.counters[0] += 2;
         } else {
-            launch_step(threads, nch, gs, (unsigned)count, smem, st, a, kb, ks);
+            launch_step(threads, nch, gs, (unsigned)known, smem, st, a, kb, ks);
             L.counters[0]++;
         }
         L.end(span);
         L.counters[3]++;
-        SSB_CUDA(cudaMemcpyAsync(h_count, next_count, sizeof(int), cudaMemcpyDeviceToHost, st));
-        SSB_CUDA(cudaStreamSynchronize(st));
-        count = (size_t)*h_count;
+        SSB_CUDA(cudaMemcpyAsync(h_counts + it, d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, st));
+        SSB_CUDA(cudaEventRecord(L.count_events[it % (RUN_AHEAD + 1)], st));
         cur ^= 1;
-        tc_cur = tc_next;
     }
     SSB_CUDA(cudaStreamSynchronize(st));
+    for (uint32_t it = 1; it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
 }
 
 // folds a lane's counters and event-timed spans into the handle (stream already synchronised)
@@ -437,10 +456,10 @@ double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int 
                                                              L.Pinv[0].template as<float>(), Mp, split);
     }
     SSB_CUDA(cudaGetLastError());
-    contract(L, tc, 0, rows);   // warm-up + the result
+    contract(L, tc, 0, rows, nullptr, true);   // warm-up + the result
     cudaEvent_t e0 = L.event(), e1 = L.event();
     SSB_CUDA(cudaEventRecord(e0, L.stream));
-    for (int i = 0; i < reps; ++i) contract(L, tc, 0, rows);
+    for (int i = 0; i < reps; ++i) contract(L, tc, 0, rows, nullptr, true);
     SSB_CUDA(cudaEventRecord(e1, L.stream));
     SSB_CUDA(cudaMemcpy2DAsync(Q, N * sizeof(T), L.Q.p, Npad * sizeof(T), N * sizeof(T), rows, cudaMemcpyDeviceToHost, L.stream));
     SSB_CUDA(cudaStreamSynchronize(L.stream));

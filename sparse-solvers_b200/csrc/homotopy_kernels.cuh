@@ -49,6 +49,7 @@ struct HomArgs {
     const int* act;   // [rows]      position -> signal (nullptr: identity)
     int* act_next;    // compacted list for the next iteration
     int* next_count;
+    const int* count_in;   // signals entering this iteration, on the device (nullptr: the grid is exact)
     uint32_t* pick;   // [Bc]        atom chosen by the min-gamma search (split kernels: scan -> algebra)
     T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
     T* Pn_lo;         //             lo part (only when split != 0)
@@ -301,6 +302,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     T* s_G = reinterpret_cast<T*>(mask + ((mask_words + 3) & ~3));
 
     const int pos = blockIdx.x;
+    if (a.count_in && pos >= *a.count_in) return;   // grid sized from a stale (larger) count
     const int s = a.act ? a.act[pos] : pos;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 

@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     const int mask_words = (a.ldc + 31) >> 5;
 
     const int pos = blockIdx.x;
+    if (a.count_in && pos >= *a.count_in) return;   // grid sized from a stale (larger) count
     const int s = a.act ? a.act[pos] : pos;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     T* c = a.C + (size_t)s * a.ldc;

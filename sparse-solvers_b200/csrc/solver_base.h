@@ -77,7 +77,8 @@ struct TcPlan;   // holds the TMA descriptors of one (At, P, Q) buffer set
 TcPlan* tc_plan_create(bool f16, const void* At_hi, const void* At_lo, int n_pad, int mp, const void* P_hi, const void* P_lo,
                        int rows_alloc, const float* a_inv, const float* p_inv);
 void tc_plan_destroy(TcPlan*);
-void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream);
+// rows is an upper bound when rows_dev (device int) is given: the kernel uses min(rows, *rows_dev)
+void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev = nullptr);
 bool tc_supported(int n_pad, int mp);
 
 }  // namespace ssb
