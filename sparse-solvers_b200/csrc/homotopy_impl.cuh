@@ -409,7 +409,9 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     size_t chunk; int nlanes;
     plan_batch(batch, kmax, true, chunk, nlanes);
     // smaller pieces on the host path: one lane's copies overlap the other lane's kernels
-    if (batch >= 8192) chunk = std::min<size_t>(chunk, std::max<size_t>(2048, round_up(batch / 8, 256)));
+    size_t pieces = 4;   // C2: 2 and 4 pieces 46.4 ms/step, 16 pieces 53.4 (thin contraction waves, more tails)
+    if (const char* e = getenv("SSB200_HOST_PIECES")) pieces = (size_t)std::max(1, atoi(e));            // tuning knob
+    if (batch >= 8192) chunk = std::min<size_t>(chunk, std::max<size_t>(2048, round_up(batch / pieces, 256)));
     const size_t nchunks = (batch + chunk - 1) / chunk;
     nlanes = (int)std::min<size_t>(nlanes, nchunks);
     for (int li = 0; li < nlanes; ++li) {
