@@ -134,7 +134,11 @@ private:
     struct Lane {
         cudaStream_t stream = nullptr;
         dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, act[2], counts;
-        dev_buffer stY, stX, stIt, stErr;     // staging for the host-pointer entry points
+        // host-pointer entry: double-buffered staging and the stream its copy-outs run on
+        dev_buffer stY[2], stX[2], stIt[2], stErr[2];
+        cudaStream_t copy_out = nullptr;
+        cudaEvent_t ev_out[2] = { nullptr, nullptr };
+        int toggle = 0;
         pinned_buffer h_count;
         TcPlan* plan[2] = { nullptr, nullptr };
         bool plan_f16 = false;            // container flavour the plans were built for
@@ -145,13 +149,17 @@ private:
         struct span { cudaEvent_t a, b; int cls; };
         std::vector<span> spans;
         std::vector<cudaEvent_t> pool;
-        std::vector<cudaEvent_t> count_events;   // one per iteration in flight (count read-back)
+        std::vector<cudaEvent_t> count_events, iter_events;   // one pair per iteration in flight (count read-back)
+        cudaStream_t side = nullptr;                          // the read-backs' own stream
         Lane() { SSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
         ~Lane() {
             drop_plans();
             for (auto e : pool) cudaEventDestroy(e);
             for (auto e : count_events) cudaEventDestroy(e);
+            for (auto e : iter_events) cudaEventDestroy(e);
+            if (side) cudaStreamDestroy(side);
             for (auto& s : spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+            if (copy_out) { cudaStreamDestroy(copy_out); cudaEventDestroy(ev_out[0]); cudaEventDestroy(ev_out[1]); }
             if (stream) cudaStreamDestroy(stream);
         }
         void drop_plans() { for (auto& p : plan) { if (p) tc_plan_destroy(p); p = nullptr; } }

@@ -269,17 +269,23 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
 
     // Lockstep loop.  The number of signals still running lives on the device: counts[it] is appended to by iteration
     // it and read by iteration it + 1 (every kernel bounds itself by it), so the host never has to wait for an
-    // iteration before queueing the next.  It reads the counts back asynchronously, sizes the grids from the newest one
+    // iteration before queueing the next.  The read-backs travel on a side stream: behind another lane's bulk copy-out a
+    // 4-byte copy can wait milliseconds, and on the main stream that wait would stall the kernels behind it.  It reads the counts back asynchronously, sizes the grids from the newest one
     // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
     // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
-    constexpr uint32_t RUN_AHEAD = 2;
+    constexpr uint32_t RUN_AHEAD = 8;
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
     int* d_counts = L.counts.template as<int>();        // [max_iter + 2]
     int* h_counts = L.h_count.template as<int>();       // pinned mirror
     SSB_CUDA(cudaMemsetAsync(d_counts, 0, ((size_t)max_iter + 2) * sizeof(int), st));
     h_counts[0] = (int)rows;
     SSB_CUDA(cudaMemcpyAsync(d_counts, h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
-    while (L.count_events.size() < RUN_AHEAD + 1) { cudaEvent_t e; SSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); L.count_events.push_back(e); }
+    while (L.count_events.size() < RUN_AHEAD + 1) {
+        cudaEvent_t e, f;
+        SSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); L.count_events.push_back(e);
+        SSB_CUDA(cudaEventCreateWithFlags(&f, cudaEventDisableTiming)); L.iter_events.push_back(f);
+    }
+    if (!L.side) SSB_CUDA(cudaStreamCreateWithFlags(&L.side, cudaStreamNonBlocking));
     const bool async = tc;
     size_t known = rows;         // newest count the host has seen (upper bound of the current one)
     uint32_t seen = 0;           // ... which is counts[seen]
@@ -322,11 +328,14 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         }
         L.end(span);
         L.counters[3]++;
-        SSB_CUDA(cudaMemcpyAsync(h_counts + it, d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, st));
-        SSB_CUDA(cudaEventRecord(L.count_events[it % (RUN_AHEAD + 1)], st));
+        SSB_CUDA(cudaEventRecord(L.iter_events[it % (RUN_AHEAD + 1)], st));
+        SSB_CUDA(cudaStreamWaitEvent(L.side, L.iter_events[it % (RUN_AHEAD + 1)], 0));
+        SSB_CUDA(cudaMemcpyAsync(h_counts + it, d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, L.side));
+        SSB_CUDA(cudaEventRecord(L.count_events[it % (RUN_AHEAD + 1)], L.side));
         cur ^= 1;
     }
     SSB_CUDA(cudaStreamSynchronize(st));
+    SSB_CUDA(cudaStreamSynchronize(L.side));
     for (uint32_t it = 1; it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
 }
 
@@ -406,34 +415,66 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     if (batch == 0) return;
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
-    size_t chunk; int nlanes;
-    plan_batch(batch, kmax, true, chunk, nlanes);
-    // smaller pieces on the host path: one lane's copies overlap the other lane's kernels
-    size_t pieces = 4;   // C2: 2 and 4 pieces 46.4 ms/step, 16 pieces 53.4 (thin contraction waves, more tails)
-    if (const char* e = getenv("SSB200_HOST_PIECES")) pieces = (size_t)std::max(1, atoi(e));            // tuning knob
-    if (batch >= 8192) chunk = std::min<size_t>(chunk, std::max<size_t>(2048, round_up(batch / pieces, 256)));
-    const size_t nchunks = (batch + chunk - 1) / chunk;
-    nlanes = (int)std::min<size_t>(nlanes, nchunks);
+    size_t cap; int nlanes;
+    plan_batch(batch, kmax, true, cap, nlanes);
+
+    // The batch is cut into tapering pieces dealt to two lanes (host threads with their own stream and workspace): one
+    // lane's copy-in, thin tail iterations and launch gaps hide under the other's kernels, and each lane's copy-out runs
+    // on its own stream under that lane's next piece (double-buffered staging).  Exposed: the first copy-in and the last
+    // two, small, copy-outs.  C2 (tools/e2e_probe.py): one piece 47.9 ms/step, of which 2.5 copy-in and 7 copy-out.
+    std::vector<size_t> sizes;
+    {
+        static const double taper[] = { 0.25, 0.25, 0.1875, 0.1875, 0.0625, 0.0625 };
+        size_t left = batch;
+        if (const char* e = getenv("SSB200_HOST_PIECES")) {                                            // tuning knob: equal pieces
+            const size_t n = (size_t)std::max(1, atoi(e)), per = std::min(cap, round_up((batch + n - 1) / n, 256));
+            while (left) { sizes.push_back(std::min(per, left)); left -= sizes.back(); }
+        } else if (batch >= 16384) {
+            for (double f : taper) {
+                const size_t want = std::min(std::min(cap, round_up((size_t)(f * (double)batch), 256)), left);
+                if (want) { sizes.push_back(want); left -= want; }
+            }
+            while (left) { sizes.push_back(std::min(cap, left)); left -= sizes.back(); }
+        } else {
+            while (left) { sizes.push_back(std::min(cap, left)); left -= sizes.back(); }
+        }
+    }
+    const size_t big = *std::max_element(sizes.begin(), sizes.end());
+    std::vector<size_t> start(sizes.size() + 1, 0);
+    for (size_t c = 0; c < sizes.size(); ++c) start[c + 1] = start[c] + sizes[c];
+    nlanes = (int)std::min<size_t>(nlanes, sizes.size());
     for (int li = 0; li < nlanes; ++li) {
         Lane& L = lane(li);
-        reserve_workspace(L, chunk, kmax);
-        L.stY.reserve(chunk * M * sizeof(T));
-        L.stX.reserve(chunk * N * sizeof(T));
-        L.stIt.reserve(chunk * sizeof(uint32_t));
-        L.stErr.reserve(chunk * sizeof(double));
+        reserve_workspace(L, big, kmax);
+        if (!L.copy_out) {
+            SSB_CUDA(cudaStreamCreateWithFlags(&L.copy_out, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) SSB_CUDA(cudaEventCreateWithFlags(&L.ev_out[i], cudaEventDisableTiming));
+        }
+        for (int i = 0; i < 2; ++i) {
+            L.stY[i].reserve(big * M * sizeof(T));
+            L.stX[i].reserve(big * N * sizeof(T));
+            L.stIt[i].reserve(big * sizeof(uint32_t));
+            L.stErr[i].reserve(big * sizeof(double));
+        }
+        L.toggle = 0;
     }
-    run_lanes(nlanes, nchunks, [&](Lane& L, size_t c) {
-        const size_t b0 = c * chunk, rows = std::min(chunk, batch - b0);
-        SSB_CUDA(cudaMemcpy2DAsync(L.stY.p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
+    const bool nocopy = getenv("SSB200_HOST_NOCOPY") != nullptr;                                       // timing experiment
+    run_lanes(nlanes, sizes.size(), [&](Lane& L, size_t c) {
+        const int b = L.toggle; L.toggle ^= 1;
+        const size_t b0 = start[c], rows = sizes[c];
+        SSB_CUDA(cudaStreamWaitEvent(L.stream, L.ev_out[b], 0));   // the piece before last has left this staging pair
+        SSB_CUDA(cudaMemcpy2DAsync(L.stY[b].p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
                                    cudaMemcpyHostToDevice, L.stream));
-        solve_chunk(L, L.stY.template as<T>(), rows, M, tol, max_iter, L.stX.template as<T>(), N,
-                    L.stIt.template as<uint32_t>(), L.stErr.template as<double>());
-        SSB_CUDA(cudaMemcpy2DAsync(X + b0 * ldx, ldx * sizeof(T), L.stX.p, N * sizeof(T), N * sizeof(T), rows,
-                                   cudaMemcpyDeviceToHost, L.stream));
-        SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt.p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream));
-        SSB_CUDA(cudaMemcpyAsync(errs + b0, L.stErr.p, rows * sizeof(double), cudaMemcpyDeviceToHost, L.stream));
-        SSB_CUDA(cudaStreamSynchronize(L.stream));
+        solve_chunk(L, L.stY[b].template as<T>(), rows, M, tol, max_iter, L.stX[b].template as<T>(), N,
+                    L.stIt[b].template as<uint32_t>(), L.stErr[b].template as<double>());   // returns with the stream drained
+        if (nocopy) return;
+        SSB_CUDA(cudaMemcpy2DAsync(X + b0 * ldx, ldx * sizeof(T), L.stX[b].p, N * sizeof(T), N * sizeof(T), rows,
+                                   cudaMemcpyDeviceToHost, L.copy_out));
+        SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt[b].p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.copy_out));
+        SSB_CUDA(cudaMemcpyAsync(errs + b0, L.stErr[b].p, rows * sizeof(double), cudaMemcpyDeviceToHost, L.copy_out));
+        SSB_CUDA(cudaEventRecord(L.ev_out[b], L.copy_out));
     });
+    for (int li = 0; li < nlanes; ++li) SSB_CUDA(cudaStreamSynchronize(lane(li).copy_out));
 }
 
 template <typename T>
