@@ -133,7 +133,7 @@ private:
     // path, its H2D / D2H copies).
     struct Lane {
         cudaStream_t stream = nullptr;
-        dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, act[2], counts;
+        dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, mask, act[2], counts;
         // host-pointer entry: double-buffered staging and the stream its copy-outs run on
         dev_buffer stY[2], stX[2], stIt[2], stErr[2];
         cudaStream_t copy_out = nullptr;

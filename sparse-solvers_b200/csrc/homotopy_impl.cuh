@@ -101,6 +101,7 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
     L.lam.reserve(r * sizeof(T));
     L.K.reserve(r * sizeof(int));
     L.pick.reserve(r * sizeof(uint32_t));
+    L.mask.reserve(r * (size_t)(Npad / 32) * sizeof(uint32_t));
     L.counts.reserve(4096 * sizeof(int));
     L.h_count.reserve(4096 * sizeof(int));
     SSB_CUDA(cudaStreamSynchronize(L.stream));
@@ -169,10 +170,10 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
 
 
 template <typename T>
-static void launch_scan(int threads, int nch, unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a)
+static void launch_scan(int threads, int nch, unsigned grid, cudaStream_t st, const HomArgs<T>& a, int kb)
 {
 #define SSB_SCAN(TH, NC)                                                                          \
-    if (threads == TH && nch == NC) { homotopy_scan_kernel<T, TH, NC><<<grid, TH, smem, st>>>(a); SSB_CUDA(cudaGetLastError()); return; }
+    if (threads == TH && nch == NC) { homotopy_scan_kernel<T, TH, NC><<<grid, TH, 0, st>>>(a, kb); SSB_CUDA(cudaGetLastError()); return; }
     SSB_SCAN(128, 1) SSB_SCAN(128, 2) SSB_SCAN(128, 4) SSB_SCAN(256, 1) SSB_SCAN(256, 2) SSB_SCAN(256, 4) SSB_SCAN(256, 0)
 #undef SSB_SCAN
     throw invalid_argument{ "no scan-kernel variant for this shape" };
@@ -214,7 +215,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     a.At = At_; a.G = G_; a.ldg = Npad;
     a.C = L.C.template as<T>(); a.Q = L.Q.template as<T>(); a.X = dX; a.ldx = ldx;
     a.gam = L.gam.template as<uint32_t>(); a.dG = L.dG.template as<T>(); a.Ginv = L.Ginv.template as<T>();
-    a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>(); a.pick = L.pick.template as<uint32_t>();
+    a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>(); a.pick = L.pick.template as<uint32_t>(); a.mask = L.mask.template as<uint32_t>();
     a.iters = d_iters; a.errs = d_errs;
     const int tc_split = tc ? (use_f16() ? 2 : 1) : 0;
     a.split = tc_split;
@@ -319,7 +320,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const int aw = (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
         if (aw > 0) {
-            launch_scan(threads, nch, (unsigned)known, homotopy_scan_smem<T>(L.ws_kmax, Npad), st, a);
+            launch_scan(threads, nch, (unsigned)known, st, a, kb);
             launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
             L.counters[0] += 2;
         } else {

@@ -50,6 +50,7 @@ struct HomArgs {
     int* act_next;    // compacted list for the next iteration
     int* next_count;
     const int* count_in;   // signals entering this iteration, on the device (nullptr: the grid is exact)
+    uint32_t* mask;   // [Bc][ldc/32] membership bits of the active set (kept by init / algebra / step, read by the scan)
     uint32_t* pick;   // [Bc]        atom chosen by the min-gamma search (split kernels: scan -> algebra)
     T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
     T* Pn_lo;         //             lo part (only when split != 0)
@@ -242,6 +243,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
         }
     }
     __syncthreads();
+    if (a.mask) {
+        const uint32_t g = s_gam[0];
+        for (int w = tid; w < (a.ldc >> 5); w += THREADS) a.mask[(size_t)s * (a.ldc >> 5) + w] = (w == (int)(g >> 5)) ? 1u << (g & 31) : 0u;
+    }
     write_rhs<T, THREADS>(a, s, s_gam, s_d, 1);
 }
 
@@ -603,6 +608,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     if (tid == 0) {
         a.lam[s] = lam_new;
         a.Kcur[s] = Knew;
+        if (a.mask) a.mask[(size_t)s * (a.ldc >> 5) + (idx >> 5)] ^= 1u << (idx & 31);
         if (cont) {
             const int row = atomicAdd(a.next_count, 1);
             a.act_next[row] = s;

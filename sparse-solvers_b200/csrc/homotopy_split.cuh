@@ -17,22 +17,32 @@
 
 namespace ssb {
 
+// (value, index) min across the warp; bit 31 of the index marks a LEAVE candidate and does not take part in the order
+// (an atom is either active or not, so two candidates never share the other 31 bits)
+template <typename T>
+__device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        T ov = __shfl_xor_sync(0xffffffffu, v, o);
+        uint32_t oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (cand_less(ov, oi & 0x7fffffffu, v, i & 0x7fffffffu)) { v = ov; i = oi; }
+    }
+}
+
+// The kernel is bound by the dependent round trips of one CTA times the CTAs an SM holds, so everything is fetched in
+// two: position -> signal, then c, q, the membership bits of this thread's atoms (a per-signal bitmask kept in HBM by
+// the algebra kernel), K, lambda and -- speculatively, for every slot below the iteration's bound kb -- the active set
+// and its direction; x at the active atoms follows while c and q are still arriving.  No shared-memory staging: slot k
+// lives in thread k % THREADS.  Three block barriers: two for the argmin, one for |c|_inf.
 template <typename T, int THREADS, int NCH>
-__global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a)
+__global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a, int kb)
 {
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ T red_v[NW];
     __shared__ uint32_t red_i[NW];
     __shared__ T sh_gamma;
     __shared__ uint32_t sh_idx;
-
-    const int KC = (a.Kmax + 2) & ~1;
-    T* s_d = reinterpret_cast<T*>(smem_raw);
-    uint32_t* s_gam = reinterpret_cast<uint32_t*>(s_d + KC);
-    uint32_t* mask = s_gam + KC;
-    const int mask_words = (a.ldc + 31) >> 5;
 
     const int pos = blockIdx.x;
     if (a.count_in && pos >= *a.count_in) return;   // grid sized from a stale (larger) count
@@ -41,10 +51,11 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     T* c = a.C + (size_t)s * a.ldc;
     const T* q = a.Q + (size_t)pos * a.ldc;
     T* x = a.X + (size_t)s * a.ldx;
+    const uint32_t* maskg = a.mask + (size_t)s * (a.ldc >> 5);
     const T TMAX = num_traits<T>::max();
 
-    // one round trip: c and q into registers, the active set and its direction into shared memory
     T cv[NCH > 0 ? NCH : 1][V], qv[NCH > 0 ? NCH : 1][V];
+    uint32_t mwr[NCH > 0 ? NCH : 1];
     if constexpr (NCH > 0) {
 #pragma unroll
         for (int ch = 0; ch < NCH; ++ch) {
@@ -52,34 +63,33 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             if (i0 < a.ldc) {
                 *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(c + i0);
                 *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
+                mwr[ch] = maskg[i0 >> 5];
             }
         }
     }
     const int K = a.Kcur[s];
     const T lam = a.lam[s];
-    for (int k = tid; k < K; k += THREADS) { s_gam[k] = a.gam[(size_t)s * a.Kmax + k]; s_d[k] = a.dG[(size_t)s * a.Kmax + k]; }
-    for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
-    __syncthreads();
     constexpr int KR = 3;   // K <= KR * THREADS (checked by the host)
-    T xk[KR];
+    uint32_t gk[KR];
+    T dk[KR], xk[KR];
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
-        if (k < K) {
-            const uint32_t g = s_gam[k];
-            atomicOr(&mask[g >> 5], 1u << (g & 31));
-            xk[u] = x[g];
-        }
+        if (k < kb) { gk[u] = a.gam[(size_t)s * a.Kmax + k]; dk[u] = a.dG[(size_t)s * a.Kmax + k]; }
     }
-    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < KR; ++u) {
+        const int k = tid + u * THREADS;
+        if (k < K) xk[u] = x[gk[u]];
+    }
 
     // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index.
     // float32 candidates are compared as integer keys bits(t) - 1 (see homotopy_step_kernel).
     T best = TMAX;
     uint32_t bidx = 0xffffffffu;
     uint32_t bestkey = __float_as_uint(FLT_MAX) - 1u;
-    auto scan = [&](const T (&cc)[V], const T (&qq)[V], int i0) {
-        const uint32_t mw = mask[i0 >> 5] >> (i0 & 31);
+    auto scan = [&](const T (&cc)[V], const T (&qq)[V], int i0, uint32_t mword) {
+        const uint32_t mw = mword >> (i0 & 31);
         if constexpr (sizeof(T) == 4) {
             uint32_t key[V];
 #pragma unroll
@@ -112,14 +122,14 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
 #pragma unroll
         for (int ch = 0; ch < NCH; ++ch) {
             const int i0 = (ch * THREADS + tid) * V;
-            if (i0 < a.N) scan(cv[ch], qv[ch], i0);
+            if (i0 < a.N) scan(cv[ch], qv[ch], i0, mwr[ch]);
         }
     } else {
         for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
             T cc[V], qq[V];
             *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
             *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
-            scan(cc, qq, i0);
+            scan(cc, qq, i0, maskg[i0 >> 5]);
         }
     }
     if constexpr (sizeof(T) == 4) best = bidx == 0xffffffffu ? TMAX : __uint_as_float(bestkey + 1u);
@@ -127,28 +137,28 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     for (int u = 0; u < KR; ++u) {   // leave candidates, -x_i / d_i (:129-137)
         const int k = tid + u * THREADS;
         if (k < K) {
-            const uint32_t i = s_gam[k];
-            const T t = -xk[u] / s_d[k];
-            if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
+            const T t = -xk[u] / dk[u];
+            if (t > T(0) && t < TMAX && cand_less(t, gk[u], best, bidx & 0x7fffffffu)) { best = t; bidx = gk[u] | 0x80000000u; }
         }
     }
-    warp_argmin(best, bidx);
+    warp_argmin_flagged(best, bidx);
     if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
     __syncthreads();
     if (warp == 0) {
         best = lane < NW ? red_v[lane] : TMAX;
         bidx = lane < NW ? red_i[lane] : 0xffffffffu;
-        warp_argmin(best, bidx);
+        warp_argmin_flagged(best, bidx);
         if (lane == 0) {
-            if (bidx == 0xffffffffu) bidx = 0;   // no candidate: (max, 0) -- the caller toggles column 0 (:122-123)
+            // no candidate: (max, 0) -- the caller toggles column 0 (:122-123), whichever side it is on
+            if (bidx == 0xffffffffu) bidx = (maskg[0] & 1u) ? 0x80000000u : 0u;
             sh_gamma = best;
             sh_idx = bidx;
         }
     }
     __syncthreads();
     const T gamma = sh_gamma;
-    const uint32_t idx = sh_idx;
-    const bool present = (mask[idx >> 5] >> (idx & 31)) & 1u;
+    const bool present = (sh_idx >> 31) != 0;
+    const uint32_t idx = sh_idx & 0x7fffffffu;
     const int Knew = present ? K - 1 : K + 1;
     if (Knew == 0) {   // :248-249: the last atom left; x, c and lambda stay as they were
         if (tid == 0) { a.iters[s] = a.it; a.errs[s] = (double)lam; a.Kcur[s] = 0; }
@@ -159,7 +169,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
-        if (k < K) x[s_gam[k]] = xk[u] + gamma * s_d[k];
+        if (k < K) x[gk[u]] = xk[u] + gamma * dk[u];
     }
 
     // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
@@ -203,12 +213,6 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             a.Kcur[s] = Knew;
         }
     }
-}
-
-template <typename T>
-inline size_t homotopy_scan_smem(int Kmax, int ldc) {
-    const size_t mask_words = (size_t)((ldc + 31) / 32 + 3) & ~(size_t)3;
-    return (size_t)((Kmax + 2) & ~1) * (sizeof(T) + sizeof(uint32_t)) + mask_words * sizeof(uint32_t) + 16;
 }
 
 // One warp per continuing signal (row of act_next).  K <= kb before the toggle; the inverse is staged in the warp's
@@ -349,7 +353,10 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
             Ginv[(size_t)r * a.Kmax + k] = s_G[r * ks + k];
         }
     }
-    if (lane == 0) a.Kcur[s] = Knew;
+    if (lane == 0) {
+        a.Kcur[s] = Knew;
+        a.mask[(size_t)s * (a.ldc >> 5) + (idx >> 5)] ^= 1u << (idx & 31);   // membership bits read by the next scan
+    }
     __syncwarp();
 
     // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs
@@ -364,25 +371,48 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
         scale = ldexpf(1.f, e);
         if (lane == 0) a.Pn_inv[row] = ldexpf(1.f, -e);
     }
-    for (int m0 = lane * V; m0 < a.Mp; m0 += 32 * V) {
-        T acc[V];
+    // two 16-byte chunks of p per pass, four atoms per batch: 8 independent loads in flight per lane, and the active
+    // set, the direction and the row address are fetched once per atom for both chunks
+    for (int mb = lane * V; mb < a.Mp; mb += 2 * 32 * V) {
+        const bool two = mb + 32 * V < a.Mp;   // warp-uniform
+        T acc0[V], acc1[V];
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[e] = T(0);
-        for (int k0 = 0; k0 < Knew; k0 += 8) {
-            T av[8][V];
+        for (int e = 0; e < V; ++e) { acc0[e] = T(0); acc1[e] = T(0); }
+        int k = 0;
+        for (; k + 4 <= Knew; k += 4) {
+            T a0[4][V], a1[4][V];
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (k0 + u < Knew)
-                    *reinterpret_cast<int4*>(av[u]) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k0 + u] * a.Mp + m0));
+            for (int u = 0; u < 4; ++u) {
+                const T* rp = a.At + (size_t)s_gam[k + u] * a.Mp + mb;
+                *reinterpret_cast<int4*>(a0[u]) = __ldg(reinterpret_cast<const int4*>(rp));
+                if (two) *reinterpret_cast<int4*>(a1[u]) = __ldg(reinterpret_cast<const int4*>(rp + 32 * V));
+            }
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (k0 + u < Knew) {
-                    const T dk = s_d[k0 + u];
+            for (int u = 0; u < 4; ++u) {
+                const T dk = s_d[k + u];
 #pragma unroll
-                    for (int e = 0; e < V; ++e) acc[e] += av[u][e] * dk;
+                for (int e = 0; e < V; ++e) acc0[e] += a0[u][e] * dk;
+                if (two) {
+#pragma unroll
+                    for (int e = 0; e < V; ++e) acc1[e] += a1[u][e] * dk;
                 }
+            }
         }
-        store_rhs<T, V>(a.split, pn, pl, m0, acc, scale);
+        for (; k < Knew; ++k) {
+            T a0[V], a1[V];
+            const T* rp = a.At + (size_t)s_gam[k] * a.Mp + mb;
+            *reinterpret_cast<int4*>(a0) = __ldg(reinterpret_cast<const int4*>(rp));
+            if (two) *reinterpret_cast<int4*>(a1) = __ldg(reinterpret_cast<const int4*>(rp + 32 * V));
+            const T dk = s_d[k];
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc0[e] += a0[e] * dk;
+            if (two) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) acc1[e] += a1[e] * dk;
+            }
+        }
+        store_rhs<T, V>(a.split, pn, pl, mb, acc0, scale);
+        if (two) store_rhs<T, V>(a.split, pn, pl, mb + 32 * V, acc1, scale);
     }
 }
 
