@@ -149,7 +149,8 @@ int ssb200_norm_l1_f64(double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrd
  *   timing (when enabled the contraction launches are bracketed by CUDA events on the handle's
  *   stream):  ms[0] = summed contraction time, ms[1] = summed step-kernel time
  *   path: 0 = choose by batch size (product behaviour), 1 = force the SIMT contraction,
- *         2 = force the tcgen05 contraction (float32 only)
+ *         2 = force the tcgen05 contraction (float32 only; fp16 operand containers, the default flavour),
+ *         3 = force the tcgen05 contraction with tf32 operand containers (the literal 3xTF32 scheme)
  */
 int ssb200_reset_counters(void* handle);
 int ssb200_get_counters(void* handle, uint64_t counters[4]);
