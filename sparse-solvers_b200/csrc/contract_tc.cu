@@ -29,11 +29,11 @@ namespace {
 
 constexpr int TILE_ATOMS = 128;     // UMMA M
 constexpr int TILE_SIGS = 256;      // UMMA N
-// The operand stream is latency-bound, not bandwidth-bound: a stage can only be refilled after its MMAs retire, so the
-// bytes in flight are (STAGES - 1) stages.  With two 96 KB stages (BLOCK_K = 32) one stage in flight covered 70 % of
-// the tensor time; four 48 KB stages (BLOCK_K = 16, 64-byte swizzle) keep three in flight from the same shared memory.
+// K-block = one swizzle span of every operand row.  128-byte rows (64 fp16 / 32 tf32 elements): three 64 KB stages per
+// CTA in the pair kernel; 64-byte rows (-DSSB_BLOCK_K=16): six 32 KB stages.  Measured on C2 the two are within 3 %
+// (gpurun_out bench A/B, 368/359 vs 353/354 TFLOP/s), the wider rows ahead: fewer, larger TMA boxes and barriers.
 #ifndef SSB_BLOCK_K
-#define SSB_BLOCK_K 16
+#define SSB_BLOCK_K 32
 #endif
 constexpr int BLOCK_K = SSB_BLOCK_K;   // floats per K-block: 32 = one 128-byte swizzle span, 16 = one 64-byte span
 constexpr int ROW_BYTES = BLOCK_K * 4;
@@ -189,11 +189,17 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
     constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;     // operand elements per K-block
     if (rows_dev) { rows = min(rows, *rows_dev); sig_tiles = (rows + tile_sigs - 1) / tile_sigs; }   // host count may be stale (larger)
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar, tmem_empty_bar;
+    constexpr int MAX_STAGES = 8;
+    __shared__ __align__(8) uint64_t full_bar[MAX_STAGES], empty_bar[MAX_STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
 
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // stage = A_hi | A_lo | P_hi | P_lo for tile_sigs signal rows: the thin tile leaves room for more stages, and the
+    // tail iterations it serves are pure latency (16 K-blocks, one CTA per atom tile)
+    const int p_bytes = tile_sigs * ROW_BYTES;
+    const int stage_bytes = 2 * A_TILE_BYTES + 2 * p_bytes;
+    const int nstages = min(MAX_STAGES, (STAGES * STAGE_BYTES) / stage_bytes);
     // A cluster of `cs` CTAs works on cs neighbouring atom tiles of ONE signal tile: each CTA fetches 1/cs of the
     // P tile and multicasts it to all of them, so the signal operand crosses the L2 -> SM fabric once per cluster
     // (the operand stream, not the tensor pipe, is what bounded the single-CTA kernel: 61 of ~64 B/clk/SM).
@@ -203,7 +209,7 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
     const int cluster_id = blockIdx.x / cs, num_clusters = gridDim.x / cs;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], cs); }
+        for (int s = 0; s < nstages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], cs); }
         mbar_init(&tmem_full_bar, 1);
         mbar_init(&tmem_empty_bar, EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -229,19 +235,19 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
                 const int n0 = ((item % (atom_tiles / cs)) * cs + crank) * TILE_ATOMS;
                 const int r0 = (item / (atom_tiles / cs)) * tile_sigs;
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
-                    const int s = it % STAGES;
-                    mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);      // every CTA of the cluster has drained stage s
-                    uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                    const int s = it % nstages;
+                    mbar_wait(&empty_bar[s], ((it / nstages) & 1) ^ 1);      // every CTA of the cluster has drained stage s
+                    uint8_t* st = smem + (size_t)s * stage_bytes;
                     mbar_expect_tx(&full_bar[s], 2 * A_TILE_BYTES + 2 * tile_sigs * ROW_BYTES);
                     tma_load_2d(st, &map_a_hi, &full_bar[s], kb * KB_ELEMS, n0);
                     tma_load_2d(st + A_TILE_BYTES, &map_a_lo, &full_bar[s], kb * KB_ELEMS, n0);
                     uint8_t* ph = st + 2 * A_TILE_BYTES + crank * part_bytes;
                     if (cs == 1) {
                         tma_load_2d(ph, &map_p_hi, &full_bar[s], kb * KB_ELEMS, r0);
-                        tma_load_2d(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0);
+                        tma_load_2d(ph + p_bytes, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0);
                     } else {
                         tma_load_2d_mc(ph, &map_p_hi, &full_bar[s], kb * KB_ELEMS, r0 + crank * part_rows, cmask);
-                        tma_load_2d_mc(ph + P_TILE_BYTES, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0 + crank * part_rows, cmask);
+                        tma_load_2d_mc(ph + p_bytes, &map_p_lo, &full_bar[s], kb * KB_ELEMS, r0 + crank * part_rows, cmask);
                     }
                 }
             }
@@ -256,12 +262,12 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
                 mbar_wait(&tmem_empty_bar, (t & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
-                    const int s = it % STAGES;
-                    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+                    const int s = it % nstages;
+                    mbar_wait(&full_bar[s], (it / nstages) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                    uint8_t* st = smem + (size_t)s * stage_bytes;
                     const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + A_TILE_BYTES);
-                    const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + P_TILE_BYTES);
+                    const uint64_t p_hi = make_desc(st + 2 * A_TILE_BYTES), p_lo = make_desc(st + 2 * A_TILE_BYTES + p_bytes);
 #pragma unroll
                     for (int kk = 0; kk < ROW_BYTES / 32; ++kk) {                  // one UMMA K-step = 32 bytes of every row
                         const uint64_t adv = (uint64_t)(kk * 2);                   // ... in 16-byte units inside the swizzle span
@@ -329,7 +335,7 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
 constexpr int PAIR_HALF_SIGS = TILE_SIGS / 2;
 constexpr int PAIR_P_BYTES = PAIR_HALF_SIGS * ROW_BYTES;                  // 8 KB
 constexpr int PAIR_STAGE_BYTES = 2 * A_TILE_BYTES + 2 * PAIR_P_BYTES;     // 32 KB per CTA
-constexpr int PAIR_STAGES = 6;
+constexpr int PAIR_STAGES = (192 * 1024) / PAIR_STAGE_BYTES;   // 6 with 64-byte rows
 constexpr int PAIR_SMEM_BYTES = PAIR_STAGES * PAIR_STAGE_BYTES + 1024;
 
 template <bool F16>
@@ -562,7 +568,8 @@ void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, c
     const bool thin = rows <= THIN_SIGS;
     const int tile_sigs = thin ? THIN_SIGS : TILE_SIGS;
     const int sig_tiles = (rows + tile_sigs - 1) / tile_sigs;
-    const int k_blocks = p->mp / (F16 ? ROW_BYTES / 2 : ROW_BYTES / 4);
+    const int kb_elems = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;
+    const int k_blocks = (p->mp + kb_elems - 1) / kb_elems;   // the last box may reach past Mp: TMA fills it with zeros
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
