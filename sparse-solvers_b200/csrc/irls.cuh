@@ -77,7 +77,7 @@ void householder_qr(std::vector<T>& a, size_t M, size_t N, std::vector<T>& Q, st
 template <typename T>
 class Irls : public SolverBase {
 public:
-    static constexpr int THREADS = 128;
+    static constexpr int THREADS = 256;
     Irls(int dev) : SolverBase(sizeof(T) == 4 ? SolverKind::IrlsF32 : SolverKind::IrlsF64, dev) {}
 
     int M = 0, N = 0, Mp = 0, Npad = 0;

@@ -52,6 +52,49 @@ __device__ __forceinline__ T block_sum(T v, T* red) {
     return t;
 }
 
+// acc[x][y] += sum over k in [k0, k1), IN ORDER, of u(k, i) * v(k, j) for the 4 x 4 elements this thread owns in the
+// 64 x 64 tile (it, jt): i = 64 it + ti + 16 x, j = 64 jt + tj + 16 y.  Multiply and add are rounded separately, one
+// term at a time, exactly like the scalar loops they replace; the 16 chains of a thread advance together (that is what
+// fills the FP64 pipe) and each operand row is read once per tile instead of once per element.
+//   GRAM   u(k, i) = Q[k][i],  v(k, j) = Q[k][j] * w_j   (G = Q^T (Q o w), irls-cpu.cpp:47-48; rows of Qt are columns of Q)
+//   !GRAM  u(k, i) = L[i][k],  v(k, j) = L[j][k]         (left-looking Cholesky update, cholesky_decomposition.h:77)
+// Rows / columns past N and rows past M are zero padding: they add +0.
+template <typename T, int THREADS, bool GRAM>
+__device__ __forceinline__ void tile_mac(const T* __restrict__ src, int ld, int N, const T* __restrict__ w, int it, int jt,
+                                         int k0, int k1, T (&acc)[4][4], T (*sm_i)[65], T (*sm_j)[65])
+{
+    static_assert(THREADS == 256, "16 x 16 threads, 4 x 4 elements each");
+    constexpr int TB = 64, MC = 16;
+    const int tid = threadIdx.x, ti = tid & 15, tj = tid >> 4;
+    for (int kc = k0; kc < k1; kc += MC) {
+        for (int e = tid; e < TB * MC; e += THREADS) {
+            if constexpr (GRAM) {
+                const int r = e / MC, kk = e % MC;
+                const int cj = jt * TB + r;
+                sm_i[kk][r] = src[(size_t)(it * TB + r) * ld + kc + kk];
+                sm_j[kk][r] = mul_rn(src[(size_t)cj * ld + kc + kk], cj < N ? w[cj] : T(0));
+            } else {
+                const int kk = e / TB, r = e % TB;
+                const int ri = it * TB + r, rj = jt * TB + r;
+                sm_i[kk][r] = ri < N ? src[(size_t)(kc + kk) * ld + ri] : T(0);
+                sm_j[kk][r] = rj < N ? src[(size_t)(kc + kk) * ld + rj] : T(0);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < MC; ++kk) {
+            T u[4], v[4];
+#pragma unroll
+            for (int x = 0; x < 4; ++x) { u[x] = sm_i[kk][ti + 16 * x]; v[x] = sm_j[kk][tj + 16 * x]; }
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 4; ++y) acc[x][y] = add_rn(acc[x][y], mul_rn(u[x], v[y]));
+        }
+        __syncthreads();
+    }
+}
+
 template <typename T, int THREADS>
 __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
 {
@@ -60,6 +103,8 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
     __shared__ T red2[NW];
     __shared__ T sh_piv;
     __shared__ int sh_bad;
+    __shared__ T sm_i[16][65], sm_j[16][65];   // operand chunks of the Gram / Cholesky tiles
+    __shared__ T diag_acc[64];
 
     const int N = a.N;
     const size_t b = blockIdx.x;
@@ -82,16 +127,48 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
     do {
         // ---- irls_newton (:39-60).  G = Q^T (Q o w) on the lower triangle (:47-48), left-looking Cholesky.
         int bad = 0;
-        for (int j = 0; j < N; ++j) {
-            const T wj = w[j];
-            const T* qj = a.Qt + (size_t)j * a.ldq;
+        constexpr int TB = 64;
+        const int NT = (N + TB - 1) / TB;
+        const int ti = tid & 15, tj = tid >> 4;
+        // G = Q^T (Q o w), lower triangle, into L (:47-48)
+        for (int jt = 0; jt < NT; ++jt)
+            for (int it = jt; it < NT; ++it) {
+                T acc[4][4] = {};
+                tile_mac<T, THREADS, true>(a.Qt, a.ldq, N, w, it, jt, 0, a.ldq, acc, sm_i, sm_j);
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 4; ++y) {
+                        const int i = it * TB + ti + 16 * x, j = jt * TB + tj + 16 * y;
+                        if (i < N && j < N && i >= j) L[(size_t)j * N + i] = acc[x][y];
+                    }
+            }
+        __syncthreads();
+        // Left-looking Cholesky (cholesky_decomposition.h:57-86), blocked by 64 columns: the part of every element's sum
+        // that runs over finished blocks (k < 64 jt) is formed tile by tile and parked in the unused upper triangle
+        // (the diagonal in shared memory); the columns of the block then finish their sums one after the other.
+        for (int jt = 0; jt < NT; ++jt) {
+            const int kend = jt * TB;
+            if (kend > 0) {
+                for (int it = jt; it < NT; ++it) {
+                    T acc[4][4] = {};
+                    tile_mac<T, THREADS, false>(L, N, N, nullptr, it, jt, 0, kend, acc, sm_i, sm_j);
+#pragma unroll
+                    for (int x = 0; x < 4; ++x)
+#pragma unroll
+                        for (int y = 0; y < 4; ++y) {
+                            const int i = it * TB + ti + 16 * x, j = jt * TB + tj + 16 * y;
+                            if (i < N && j < N && i >= j) { if (i == j) diag_acc[j - kend] = acc[x][y]; else L[(size_t)i * N + j] = acc[x][y]; }
+                        }
+                }
+                __syncthreads();
+            }
+            const int jend = min(N, kend + TB);
+            for (int j = kend; j < jend; ++j) {
             for (int i = j + tid; i < N; i += THREADS) {
-                const T* qi = a.Qt + (size_t)i * a.ldq;
-                T g = T(0);
-                for (int m = 0; m < a.M; ++m) g = add_rn(g, mul_rn(qi[m], mul_rn(qj[m], wj)));
-                T acc = T(0);
-                for (int k = 0; k < j; ++k) acc = add_rn(acc, mul_rn(L[(size_t)k * N + i], L[(size_t)k * N + j]));
-                L[(size_t)j * N + i] = g - acc;
+                T acc = kend > 0 ? (i == j ? diag_acc[j - kend] : L[(size_t)i * N + j]) : T(0);
+                for (int k = kend; k < j; ++k) acc = add_rn(acc, mul_rn(L[(size_t)k * N + i], L[(size_t)k * N + j]));
+                L[(size_t)j * N + i] = L[(size_t)j * N + i] - acc;
             }
             __syncthreads();
             const T ajj = sqrt(L[(size_t)j * N + j]);
@@ -100,6 +177,7 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
             __syncthreads();
             for (int i = j + tid; i < N; i += THREADS) L[(size_t)j * N + i] *= inv;
             __syncthreads();
+            }
         }
         if (bad) { spd_error = 1; break; }      // :94-97, x keeps the previous iterate
 

@@ -31,7 +31,8 @@ def test_golden(ss, name):
     assert (np.argmax(X[ok], axis=1) == np.argmax(g["X"][ok], axis=1)).all()
 
 
-@pytest.mark.parametrize("dtype,m,n,k", [(np.float64, 96, 24, 2), (np.float64, 200, 64, 1), (np.float32, 80, 20, 1)])
+@pytest.mark.parametrize("dtype,m,n,k", [(np.float64, 96, 24, 2), (np.float64, 200, 64, 1), (np.float32, 80, 20, 1),
+                                          (np.float64, 700, 200, 3), (np.float32, 300, 130, 2)])   # several Gram / Cholesky tiles
 def test_vs_port(ss, dtype, m, n, k):
     from oracle import port
     rng = np.random.default_rng(m + n)
