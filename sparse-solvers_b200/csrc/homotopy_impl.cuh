@@ -193,7 +193,14 @@ static void launch_algebra_variant(unsigned rows, size_t slice, cudaStream_t st,
 }
 
 // warps per CTA of the algebra kernel for a slice size; 0 = the active set is too large for the split kernels
-static inline int algebra_warps(size_t slice) { return slice <= 24 * 1024 ? 4 : slice <= 48 * 1024 ? 2 : slice <= 96 * 1024 ? 1 : 0; }
+// The warp-per-signal algebra kernel pays off while a warp's K x K work is short: measured on C3 (K grows to 100) a slice
+// limit of 8-16 KB (K <= ~45-60) runs the step in 167-176 ms per 65,536 signals, 24 KB in 191 ms, 48 KB in 332 ms; past
+// the limit the CTA-per-signal step kernel takes over.
+static inline int algebra_warps(size_t slice) {
+    int lim = 10 * 1024;
+    if (const char* e = getenv("SSB200_ALG_SLICE")) lim = atoi(e);                                     // tuning knob
+    return slice <= (size_t)lim ? 4 : 0;
+}
 
 template <typename T>
 static void launch_algebra(int W, unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
