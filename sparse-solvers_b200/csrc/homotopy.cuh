@@ -15,6 +15,7 @@
 #include "contract_simt.cuh"
 #include "homotopy_kernels.cuh"
 #include "homotopy_split.cuh"
+#include "homotopy_single.cuh"
 #include "solver_base.h"
 
 namespace ssb {
@@ -241,6 +242,11 @@ private:
     void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                      uint32_t* d_iters, double* d_errs);
     void merge(Lane& L);
+    // one signal: the whole solve in one cooperative kernel (homotopy_single.cuh); false = shape not supported
+    bool solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters, double* errs,
+                      bool reports_on_host);
+    dev_buffer single_ws_;
+    pinned_buffer single_rep_;
     template <typename F> void run_lanes(int nlanes, size_t nchunks, F&& body);
 };
 

@@ -392,6 +392,68 @@ void Homotopy<T>::run_lanes(int nlanes, size_t nchunks, F&& body)
     for (int li = 0; li < nlanes; ++li) if (err[li]) std::rethrow_exception(err[li]);
 }
 
+
+template <typename T>
+bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters,
+                               double* errs, bool reports_on_host)
+{
+    if (contraction_path >= 2) return false;                      // a forced tensor path is honoured by the lockstep code
+    if (const char* e = getenv("SSB200_SINGLE")) if (atoi(e) == 0) return false;                       // tuning knob
+    constexpr int THREADS = 256;
+    int sms = 0, coop = 0;
+    SSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    SSB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+    if (!coop) return false;
+    const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
+    const int ks = (kmax + 1) | 1;
+    const int grid = std::min(sms, (Npad + 7) / 8);
+    const int cnt = (Npad + grid - 1) / grid;
+    const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
+    if (smem > 200 * 1024) return false;
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        SSB_CUDA(cudaFuncSetAttribute(homotopy_single_kernel<T, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = 200 * 1024;
+    }
+    Lane& L = lane(0);
+    cudaStream_t st = L.stream;
+    // workspace: y (padded) | P | Cg | x | part_t | part_max | part_i | iters | errs
+    const size_t nT = (size_t)2 * Mp + Npad + N + 2 * (size_t)grid + 8;
+    single_ws_.reserve(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64);
+    single_rep_.reserve(64);
+    T* w = single_ws_.template as<T>();
+    T* d_y = w; T* d_P = d_y + Mp; T* d_Cg = d_P + Mp; T* d_x = d_Cg + Npad; T* d_pt = d_x + N; T* d_pm = d_pt + grid;
+    double* d_err = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(w) + round_up((size_t)(d_pm + grid - w) * sizeof(T), 16));
+    uint32_t* d_it = reinterpret_cast<uint32_t*>(d_err + 1);
+    uint32_t* d_pi = d_it + 2;
+    if (Mp > M) SSB_CUDA(cudaMemsetAsync(d_y + M, 0, (size_t)(Mp - M) * sizeof(T), st));
+    SSB_CUDA(cudaMemcpyAsync(d_y, y, (size_t)M * sizeof(T), y_on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    SingleArgs<T> a{};
+    a.N = N; a.Npad = Npad; a.Mp = Mp; a.Kmax = kmax; a.ks = ks;
+    a.At = At_; a.G = G_; a.ldg = Npad;
+    a.y = d_y; a.x = x_on_host ? d_x : x; a.P = d_P; a.Cg = d_Cg; a.part_t = d_pt; a.part_i = d_pi; a.part_max = d_pm;
+    a.iters = reports_on_host ? d_it : iters; a.errs = reports_on_host ? d_err : errs;
+    a.tol = tol; a.max_iter = max_iter; a.cnt = cnt;
+    void* params[] = { &a };
+    const int span = L.begin(timing, 1);
+    SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS>, dim3((unsigned)grid), dim3(THREADS), params, smem, st));
+    L.end(span);
+    L.counters[0]++;
+    if (x_on_host) SSB_CUDA(cudaMemcpyAsync(x, d_x, (size_t)N * sizeof(T), cudaMemcpyDeviceToHost, st));
+    if (reports_on_host) {
+        unsigned char* h = single_rep_.template as<unsigned char>();
+        SSB_CUDA(cudaMemcpyAsync(h, d_err, 16, cudaMemcpyDeviceToHost, st));
+        SSB_CUDA(cudaStreamSynchronize(st));
+        *errs = *reinterpret_cast<double*>(h);
+        *iters = *reinterpret_cast<uint32_t*>(h + 8);
+    } else {
+        SSB_CUDA(cudaStreamSynchronize(st));
+    }
+    L.counters[3] += reports_on_host ? *iters : 0;
+    merge(L);
+    return true;
+}
+
 template <typename T>
 void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                                   uint32_t* d_iters, double* d_errs, cudaStream_t user_stream)
@@ -402,6 +464,7 @@ void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, 
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     // inputs produced on the caller's stream must be complete before the lanes read them
     SSB_CUDA(cudaStreamSynchronize(user_stream));
+    if (batch == 1 && solve_single(dY, false, tol, max_iter, dX, false, d_iters, d_errs, false)) return;
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     size_t chunk; int nlanes;
     plan_batch(batch, kmax, false, chunk, nlanes);
@@ -422,6 +485,7 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");
     if (batch == 0) return;
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
+    if (batch == 1 && solve_single(Y, true, tol, max_iter, X, true, iters, errs, true)) return;
     const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     size_t cap; int nlanes;
     plan_batch(batch, kmax, true, cap, nlanes);

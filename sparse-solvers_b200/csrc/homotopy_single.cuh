@@ -1,0 +1,307 @@
+// Single-signal latency path (BASELINE config 1): the WHOLE homotopy solve of one signal in one cooperative kernel.
+// The lockstep path spends ~35 us per iteration of one signal on two launches and a host round trip; here an iteration
+// is three grid barriers.  Every CTA owns a slice of atoms for the whole solve and keeps its slice of c on chip:
+//   phase 1  all CTAs   q = A^T p over the CTA's atoms (warp per atom, the arithmetic of contract_gemv_kernel), join
+//                       candidates of the slice; CTA 0 adds the leave candidates (homotopy-cpu.cpp:112-163)
+//   phase 2  all CTAs   (gamma, idx) = min over the CTA partials (every CTA redundantly); c -= gamma q on the slice,
+//                       partial |c|_inf, slice of c published for the signs (:252-255, :270)
+//   phase 3  CTA 0      x += gamma d, toggle, online inverse update (in shared memory for the whole solve), new d,
+//                       p = A_G d (:166-183, :259-266, online_inverse.h:183-293); all CTAs: stop test (:272)
+// Same formulas, summation orders and quirks as homotopy_step_kernel; the dictionary (1-4 MB) streams from L2.
+#pragma once
+
+#include <cooperative_groups.h>
+
+#include "homotopy_split.cuh"
+
+namespace ssb {
+
+template <typename T>
+struct SingleArgs {
+    int N, Npad, Mp, Kmax, ks;
+    const T* At; const T* G; int ldg;
+    const T* y;           // [Mp] zero padded signal
+    T* x;                 // [N] output (zeroed by the kernel)
+    T* P;                 // [Mp] scratch: current right-hand side
+    T* Cg;                // [Npad] scratch: c, published every iteration
+    T* part_t; uint32_t* part_i; T* part_max;   // [grid] partials
+    uint32_t* iters; double* errs;
+    T tol; uint32_t max_iter;
+    int cnt;              // atoms per CTA
+};
+
+template <typename T>
+inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks) {
+    const size_t KC = (size_t)((Kmax + 2) & ~1);
+    return ((size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64;
+}
+
+template <typename T, int THREADS>
+__global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> a)
+{
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    constexpr int V = 16 / sizeof(T);
+    constexpr int NW = THREADS / 32;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ T red_v[NW];
+    __shared__ uint32_t red_i[NW];
+    __shared__ T sh_gamma, sh_lam;
+    __shared__ uint32_t sh_idx;
+
+    const int KC = (a.Kmax + 2) & ~1;
+    T* s_p = reinterpret_cast<T*>(smem_raw);          // [Mp]
+    T* s_c = s_p + a.Mp;                              // [cnt]
+    T* s_q = s_c + a.cnt;                             // [cnt]
+    T* s_G = s_q + a.cnt;                             // [(Kmax+1) * ks]   CTA 0 only from here on
+    T* s_d = s_G + (size_t)(a.Kmax + 1) * a.ks;
+    T* s_u1 = s_d + KC;
+    T* s_u2 = s_u1 + KC;
+    T* s_cg = s_u2 + KC;
+    T* s_x = s_cg + KC;                               // x at the active atoms
+    uint32_t* s_act = reinterpret_cast<uint32_t*>(s_x + 2 * KC);   // [cnt] membership of the slice's atoms
+    uint32_t* s_gam = s_act + a.cnt;                  // [KC]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = blockIdx.x, G = gridDim.x;
+    const int a0 = cta * a.cnt, a1 = min(a.Npad, a0 + a.cnt);
+    const T TMAX = num_traits<T>::max();
+
+    // q over the slice: one warp per atom, lanes stride the row in 16-byte pieces, warp_sum (contract_gemv_kernel)
+    auto correlate = [&](const T* rhs) {
+        for (int n = a0 + warp; n < a1; n += NW) {
+            const T* row = a.At + (size_t)n * a.Mp;
+            T acc = T(0);
+            for (int m = lane * V; m < a.Mp; m += 32 * V) {
+                T av[V];
+                *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(row + m));
+#pragma unroll
+                for (int v = 0; v < V; ++v) acc += av[v] * rhs[m + v];
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) s_q[n - a0] = acc;
+        }
+    };
+    // block-wide lexicographic min of (value, index); bit 31 of the index may carry the leave flag
+    auto block_argmin = [&](T& v, uint32_t& i) {
+        warp_argmin_flagged(v, i);
+        if (lane == 0) { red_v[warp] = v; red_i[warp] = i; }
+        __syncthreads();
+        v = lane < NW ? red_v[lane] : TMAX;
+        i = lane < NW ? red_i[lane] : 0xffffffffu;
+        warp_argmin_flagged(v, i);
+        __syncthreads();
+    };
+
+    // ---- initial state (homotopy-cpu.cpp:201-229)
+    for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = a.y[m];
+    for (int n = a0 + tid; n < a1; n += THREADS) { s_act[n - a0] = 0u; if (n < a.N) a.x[n] = T(0); }
+    __syncthreads();
+    correlate(s_p);
+    __syncthreads();
+    {
+        T best = T(-1);
+        uint32_t bidx = 0xffffffffu;
+        for (int n = a0 + tid; n < a1; n += THREADS) {
+            s_c[n - a0] = s_q[n - a0];
+            if (n < a.N) { const T av = fabs(s_q[n - a0]); if (av > best) { best = av; bidx = (uint32_t)n; } }
+        }
+        warp_argmax_first(best, bidx);
+        if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
+            a.part_t[cta] = best; a.part_i[cta] = bidx;
+            if (cta == 0) a.part_max[0] = fabs(s_q[0]);
+        }
+    }
+    grid.sync();
+    T lam;
+    int K = 1;
+    {
+        T best = T(-1);
+        uint32_t bidx = 0xffffffffu;
+        for (int g = tid; g < G; g += THREADS) {
+            const T v = a.part_t[g]; const uint32_t i = a.part_i[g];
+            if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
+        }
+        warp_argmax_first(best, bidx);
+        if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+        __syncthreads();
+        best = red_v[0]; bidx = red_i[0];
+        for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
+        if (bidx == 0xffffffffu) { bidx = 0; best = a.part_max[0]; }   // all-NaN correlations
+        lam = best;
+        if ((int)bidx >= a0 && (int)bidx < a1 && tid == 0) s_act[bidx - a0] = 1u;
+        if (cta == 0) {
+            if (tid == 0) {
+                const T nrm = sqrt(a.G[(size_t)bidx * a.ldg + bidx]);       // online_inverse.h:193-201
+                const T inv = T(1) / (nrm * nrm);
+                s_gam[0] = bidx; s_G[0] = inv; s_d[0] = sign_tol(best, a.tol) * inv; s_x[0] = T(0);   // sign of |c|: :223-224
+            }
+            __syncthreads();
+            const T d0 = s_d[0];
+            for (int m = tid; m < a.Mp; m += THREADS) a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
+        }
+    }
+    __threadfence();
+    grid.sync();
+
+    // ---- the loop (homotopy-cpu.cpp:236-272)
+    uint32_t it = 0;
+    for (;;) {
+        ++it;
+        for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = __ldcg(a.P + m);
+        __syncthreads();
+        correlate(s_p);
+        __syncthreads();
+        // min-gamma search (:122-163): join candidates of the slice, leave candidates in CTA 0
+        T best = TMAX;
+        uint32_t bidx = 0xffffffffu;
+        for (int n = a0 + tid; n < a1 && n < a.N; n += THREADS) {
+            if (s_act[n - a0]) continue;
+            const T cc = s_c[n - a0], qq = s_q[n - a0];
+            const T dl = T(1) - qq, dr = T(1) + qq;
+            if (dl != T(0)) { const T t = step_ratio(lam - cc, dl); if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
+            if (dr != T(0)) { const T t = step_ratio(lam + cc, dr); if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
+        }
+        if (cta == 0)
+            for (int k = tid; k < K; k += THREADS) {
+                const T t = -s_x[k] / s_d[k];
+                if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
+            }
+        block_argmin(best, bidx);
+        if (tid == 0) {
+            a.part_t[cta] = best; a.part_i[cta] = bidx;
+            if (cta == 0) a.part_i[G] = s_act[0];       // membership of atom 0, for the no-candidate case
+        }
+        __threadfence();
+        grid.sync();
+
+        best = TMAX; bidx = 0xffffffffu;
+        for (int g = tid; g < G; g += THREADS) {
+            const T v = __ldcg(a.part_t + g); const uint32_t i = __ldcg(a.part_i + g);
+            if (cand_less(v, i & 0x7fffffffu, best, bidx & 0x7fffffffu)) { best = v; bidx = i; }
+        }
+        block_argmin(best, bidx);
+        if (bidx == 0xffffffffu) bidx = __ldcg(a.part_i + G) ? 0x80000000u : 0u;   // (max, 0): the caller toggles column 0 (:122-123)
+        const T gamma = best;
+        const bool present = (bidx >> 31) != 0;
+        const uint32_t idx = bidx & 0x7fffffffu;
+        const int Knew = present ? K - 1 : K + 1;
+        if (Knew == 0) {   // :248-249
+            if (cta == 0 && tid == 0) { *a.iters = it; *a.errs = (double)lam; }
+            break;
+        }
+        // c -= gamma q on the slice, |c|_inf partial (:255, :270)
+        T mx = T(0);
+        for (int n = a0 + tid; n < a1; n += THREADS) {
+            const T cn = s_c[n - a0] - gamma * s_q[n - a0];
+            s_c[n - a0] = cn;
+            a.Cg[n] = cn;
+            if (n < a.N) mx = max(mx, fabs(cn));
+        }
+        if ((int)idx >= a0 && (int)idx < a1 && tid == 0) s_act[idx - a0] ^= 1u;
+        mx = warp_max(mx);
+        if (lane == 0) red_v[warp] = mx;
+        __syncthreads();
+        if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); a.part_max[cta] = m; }
+        __threadfence();
+        grid.sync();
+
+        T lam_new = T(0);
+        for (int g = tid; g < G; g += THREADS) lam_new = max(lam_new, __ldcg(a.part_max + g));
+        lam_new = warp_max(lam_new);
+        if (lane == 0) red_v[warp] = lam_new;
+        __syncthreads();
+        lam_new = red_v[0];
+        for (int w = 1; w < NW; ++w) lam_new = max(lam_new, red_v[w]);
+        __syncthreads();
+        const bool cont = (it < a.max_iter) && (lam_new > a.tol);   // :272
+
+        if (cta == 0) {
+            const int ldm = a.ks;
+            // x += gamma * d with the OLD direction (:252)
+            for (int k = tid; k < K; k += THREADS) { const T xv = s_x[k] + gamma * s_d[k]; s_x[k] = xv; a.x[s_gam[k]] = xv; }
+            int slot = -1;
+            if (present) { for (int k = 0; k < K; ++k) if (s_gam[k] == idx) slot = k; }
+            const int ncg = K + (present ? 0 : 1);
+            for (int k = tid; k < ncg; k += THREADS) s_cg[k] = __ldcg(a.Cg + (k < K ? s_gam[k] : idx));
+            __syncthreads();
+            if (!present) {
+                // online_inverse.h:203-249 (bordering); the new atom takes slot K
+                for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];
+                const T dot = a.G[(size_t)idx * a.ldg + idx];
+                __syncthreads();
+                matvec<T, THREADS, true>(s_G, ldm, K, s_u1, s_u2, nullptr);
+                __syncthreads();
+                T uu = T(0);
+                for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
+                uu = warp_sum(uu);
+                const T dd = T(1) / (dot - uu);
+                for (int e = tid; e < K * K; e += THREADS) {
+                    const int r = e / K, k = e - r * K;
+                    s_G[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
+                }
+                for (int r = tid; r < K; r += THREADS) {
+                    const T u3 = -dd * s_u2[r];
+                    s_G[(size_t)r * ldm + K] = u3;
+                    s_G[(size_t)K * ldm + r] = u3;
+                }
+                if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = a.x[idx]; }
+            } else {
+                // online_inverse.h:253-293; the leaving atom sits in slot j
+                const int j = slot;
+                const T dd = s_G[(size_t)j * ldm + j];
+                const T sc = -(T(1) / dd);
+                __syncthreads();
+                for (int r = tid; r < K; r += THREADS) s_u1[r] = s_G[(size_t)r * ldm + j] * sc;
+                __syncthreads();
+                for (int e = tid; e < K * K; e += THREADS) {
+                    const int r = e / K, k = e - r * K;
+                    if (r != j && k != j) s_G[(size_t)r * ldm + k] += (-dd * s_u1[r]) * s_u1[k];
+                }
+                __syncthreads();
+                const int last = K - 1;
+                if (j != last) {
+                    for (int k = tid; k < last; k += THREADS) {
+                        const int kk = (k == j) ? last : k;
+                        const T vrow = s_G[(size_t)last * ldm + kk];
+                        const T vcol = s_G[(size_t)kk * ldm + last];
+                        s_G[(size_t)j * ldm + k] = vrow;
+                        s_G[(size_t)k * ldm + j] = vcol;
+                    }
+                    if (tid == 0) { s_gam[j] = s_gam[last]; s_cg[j] = s_cg[last]; s_x[j] = s_x[last]; }
+                }
+            }
+            __syncthreads();
+            // d_G = inv * sign(c_G, tol) (:259-263)
+            for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(s_cg[k], a.tol);
+            __syncthreads();
+            matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
+            __syncthreads();
+            if (cont) {   // p = A_G d (:112-116), k ascending per element as write_rhs
+                for (int m0 = tid * V; m0 < a.Mp; m0 += THREADS * V) {
+                    T acc[V];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) acc[e] = T(0);
+                    for (int k = 0; k < Knew; ++k) {
+                        T av[V];
+                        *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
+                        const T dk = s_d[k];
+#pragma unroll
+                        for (int e = 0; e < V; ++e) acc[e] += av[e] * dk;
+                    }
+                    *reinterpret_cast<int4*>(a.P + m0) = *reinterpret_cast<const int4*>(acc);
+                }
+            } else if (tid == 0) { *a.iters = it; *a.errs = (double)lam_new; }   // :274
+        }
+        K = Knew;
+        lam = lam_new;
+        if (!cont) break;
+        __threadfence();
+        grid.sync();
+    }
+}
+
+}  // namespace ssb
