@@ -30,7 +30,7 @@ import numpy as np  # noqa: E402
 
 CONFIGS = {
     # BASELINE.json configs[]; C2 is the configuration the metric is quoted on
-    "C1": dict(m=256, n=1024, k=16, dtype="float32", batch=1024, tol=1e-3, max_iter=48),
+    "C1": dict(m=256, n=1024, k=16, dtype="float32", batch=1024, tol=1e-3, max_iter=48, solver="single"),
     "C2": dict(m=512, n=2048, k=32, dtype="float32", batch=65536, tol=1e-3, max_iter=80),
     "C3": dict(m=504, n=1216, k=32, dtype="float32", batch=262144, tol=1e-3, max_iter=100, synth="face"),
     # BASELINE says 1024x4096; the reference's IRLS is undefined for M < N: the tall reading is the oracle-able one
@@ -212,6 +212,51 @@ def run_irls(args, cfg):
     print(json.dumps(line))
 
 
+def run_single(args, cfg):
+    """C1: the single-signal latency path -- `batch` signals solved ONE CALL AT A TIME through the reference-shaped
+    solve(y) entry (host buffers in and out, so `value` and `e2e` are the same measurement)."""
+    import torch
+    import sparsesolvers as ss
+    batch = args.batch or cfg["batch"]
+    A, Y = make_workload(cfg, batch, seed=4321)
+    solver = ss.Homotopy(A)
+    for b in range(min(batch, 16 * max(1, args.warmup))):
+        solver.solve(Y[b], cfg["tol"], cfg["max_iter"])
+    torch.cuda.synchronize()
+    its = np.empty(batch)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for b in range(batch):
+            x, rep = solver.solve(Y[b], cfg["tol"], cfg["max_iter"])
+            its[b] = rep.iter
+    secs = time.perf_counter() - t0
+    M, N = cfg["m"], cfg["n"]
+    value = batch * args.steps / secs
+    peaks, peak_src = measured_peaks()
+    nbytes = 4.0 * M * N * (its.mean() + 1) * batch * args.steps            # one pass over A per iteration + the initial one
+    cpu = None
+    if not args.no_cpu_baseline:
+        sample = min(batch, args.cpu_sample or 256)
+        from oracle import ref
+        if ref.available():
+            ref.set_blas_threads(1)
+            t1 = time.perf_counter(); Xr, itr, er = ref.homotopy(A, Y[:sample], cfg["tol"], cfg["max_iter"], threads=1); dt = time.perf_counter() - t1
+            cpu = {"value": sample / dt, "unit": "signals/s", "cores": 1, "kind": "reference",
+                   "sample": f"first {sample} signals, one call at a time, 1 thread, {dt:.2f} s", "iters_match_gpu": int((itr == its[:sample]).sum())}
+    line = {"metric": "homotopy signals/sec (single-signal calls)", "value": value, "unit": "signals/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C1: homotopy A {M}x{N} float32, k={cfg['k']}, tol {cfg['tol']}, max_iter {cfg['max_iter']}, {batch} signals one call each",
+                       "mean_iters": float(its.mean()), "us_per_iteration": 1e6 * secs / (args.steps * batch * (its.mean() + 1))},
+            "e2e": {"value": value, "unit": "signals/s", "h2d_bytes_per_step": batch * M * 4, "d2h_bytes_per_step": batch * (N * 4 + 12)},
+            "gpu_launches": solver.counters()["launches"],
+            "roofline": {"kernel": "homotopy_single_kernel", "bound": "hbm", "achieved": nbytes / secs / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": nbytes / secs / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                         "note": "A (1 MB) is L2-resident: the bound that bites is three grid barriers + call overhead per iteration, not bandwidth"},
+            "cpu_baseline": cpu}
+    print(json.dumps(line))
+
+
 def run_b200(args, cfg):
     import torch
     import torch.distributed as dist
@@ -383,6 +428,8 @@ def main():
         run_reference(args, cfg)
     elif cfg.get("solver") == "irls":
         run_irls(args, cfg)
+    elif cfg.get("solver") == "single":
+        run_single(args, cfg)
     else:
         run_b200(args, cfg)
 

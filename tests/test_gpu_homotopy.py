@@ -55,6 +55,23 @@ def test_vs_port(ss, dtype, m, n, k, batch, path):
     print(stats, s.counters())
 
 
+@pytest.mark.parametrize("name", HOMOTOPY_GOLDEN)
+def test_golden_one_call_per_signal(ss, name):
+    """The single-signal entry (one cooperative kernel per solve, homotopy_single.cuh) against the reference's outputs,
+    quirk set included; 48 signals per fixture."""
+    g = np.load(os.path.join(GOLDEN, name))
+    A = np.asfortranarray(g["A"]) if "colmajor" in name else g["A"]
+    s = ss.Homotopy(A)
+    n = min(48, len(g["Y"]))
+    X = np.empty((n, A.shape[1]), dtype=A.dtype); it = np.empty(n, dtype=np.uint32); err = np.empty(n)
+    for b in range(n):
+        X[b], rep = s.solve(g["Y"][b], float(g["tol"]), int(g["max_iter"]))
+        it[b], err[b] = rep.iter, rep.solution_error
+    assert s.counters()["launches"] <= 3 + n, "the single-signal kernel did not run"
+    r = parity.compare(X, it, err, g["X"][:n], g["iters"][:n], g["errs"][:n], c0_inf(g["A"], g["Y"][:n]))
+    print(parity.assert_parity(r, A.dtype, name + " [single]"))
+
+
 def test_single_solve_equals_batch_row(ss):
     from sparsesolvers import synth
     A = synth.dictionary(64, 256, dtype=np.float32, seed=1)
