@@ -170,10 +170,13 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
 
 
 template <typename T>
-static void launch_scan(int threads, int nch, unsigned grid, cudaStream_t st, const HomArgs<T>& a, int kb)
+static void launch_scan(int threads, int nch, bool gram, unsigned grid, cudaStream_t st, const HomArgs<T>& a, int kb)
 {
 #define SSB_SCAN(TH, NC)                                                                          \
-    if (threads == TH && nch == NC) { homotopy_scan_kernel<T, TH, NC><<<grid, TH, 0, st>>>(a, kb); SSB_CUDA(cudaGetLastError()); return; }
+    if (threads == TH && nch == NC) {                                                             \
+        if (gram) homotopy_scan_kernel<T, TH, NC, true><<<grid, TH, 0, st>>>(a, kb);              \
+        else      homotopy_scan_kernel<T, TH, NC, false><<<grid, TH, 0, st>>>(a, kb);             \
+        SSB_CUDA(cudaGetLastError()); return; }
     SSB_SCAN(128, 1) SSB_SCAN(128, 2) SSB_SCAN(128, 4) SSB_SCAN(256, 1) SSB_SCAN(256, 2) SSB_SCAN(256, 4) SSB_SCAN(256, 0)
 #undef SSB_SCAN
     throw invalid_argument{ "no scan-kernel variant for this shape" };
@@ -282,6 +285,10 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
     // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
     constexpr uint32_t RUN_AHEAD = 8;
+    uint32_t gram_iters = 16;                                    // iterations 1 .. gram_iters - 1 take q from the Gram matrix
+    if (const char* e = getenv("SSB200_GRAM_ITERS")) gram_iters = (uint32_t)std::max(0, std::min(32, atoi(e)));   // tuning knob
+    if (!split_ok || nch == 0 || algebra_warps(homotopy_algebra_slice<T>((int)gram_iters, ((int)gram_iters + 1) | 1)) == 0) gram_iters = 0;
+    gram_iters = std::min<uint32_t>(gram_iters, (uint32_t)L.ws_kmax);
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
     int* d_counts = L.counts.template as<int>();        // [max_iter + 2]
     int* h_counts = L.h_count.template as<int>();       // pinned mirror
@@ -309,7 +316,12 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         }
         if (known == 0) break;
         last = it;
-        contract(L, tc, cur, known, async ? d_counts + (it - 1) : nullptr);
+        // While the active set is small (K <= it < gram_iters) q = G[:, active] d costs K rows of G per signal in the
+        // scan kernel -- less than a contraction, a K-atom gather and 16 KB of Q traffic.  Which iterations take that
+        // route depends on the iteration number alone, so a signal's arithmetic does not depend on its batch.
+        const bool gram = it < gram_iters;
+        a.skip_rhs = (it + 1 < gram_iters) ? 1 : 0;
+        if (!gram) contract(L, tc, cur, known, async ? d_counts + (it - 1) : nullptr);
         a.split = tc ? tc_split : 0;
         a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
         a.act_next = L.act[cur ^ 1].template as<int>();
@@ -324,10 +336,10 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
         SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
         const size_t slice = homotopy_algebra_slice<T>(kb, ks);
-        const int aw = (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
+        const int aw = (gram || a.skip_rhs) ? 4 : (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
         if (aw > 0) {
-            launch_scan(threads, nch, (unsigned)known, st, a, kb);
+            launch_scan(threads, nch, gram, (unsigned)known, st, a, kb);
             launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
             L.counters[0] += 2;
         } else {
@@ -344,7 +356,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     }
     SSB_CUDA(cudaStreamSynchronize(st));
     SSB_CUDA(cudaStreamSynchronize(L.side));
-    for (uint32_t it = 1; it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
+    for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
 }
 
 // folds a lane's counters and event-timed spans into the handle (stream already synchronised)

@@ -57,6 +57,7 @@ struct HomArgs {
     int split;        // how the right-hand sides are written: 0 full precision, 1 tf32 (hi, lo) floats, 2 fp16 (hi, lo * 2^11)
                       // of the row times a power of two (Pn / Pn_lo then point at __half arrays, row stride ldp halfs)
     float* Pn_inv;    // [rows]      split 2: 1 / scale of every right-hand side
+    int skip_rhs;     //             split kernels: do not form p (the next scan takes q from G)
     float amax;       //             split 2: max |A|, bounds |p| <= amax * sum |d|
     T tol;
     uint32_t max_iter;

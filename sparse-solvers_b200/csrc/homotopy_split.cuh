@@ -34,9 +34,15 @@ __device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
 // the algebra kernel), K, lambda and -- speculatively, for every slot below the iteration's bound kb -- the active set
 // and its direction; x at the active atoms follows while c and q are still arriving.  No shared-memory staging: slot k
 // lives in thread k % THREADS.  Three block barriers: two for the argmin, one for |c|_inf.
-template <typename T, int THREADS, int NCH>
+//   GRAMQ  q is not read from the contraction's output but formed here as q = G[:, active] d (G = A^T A, L2-resident): while
+//          the active set is small that is K rows of G per signal instead of a full 2 M N contraction, a gather of K atoms
+//          and 16 KB of Q traffic -- the host uses it for the first iterations (K <= it < gram_iters)
+template <typename T, int THREADS, int NCH, bool GRAMQ>
 __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a, int kb)
 {
+    constexpr int GRAM_KMAX = 32;
+    __shared__ uint32_t s_gq[GRAMQ ? GRAM_KMAX : 1];
+    __shared__ T s_dq[GRAMQ ? GRAM_KMAX : 1];
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;
     __shared__ T red_v[NW];
@@ -63,7 +69,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             if (i0 < a.ldc) {
                 // (evict-first loads were measured and lose 8 %: a third of q is still in L2 from the contraction)
                 *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(c + i0);
-                *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
+                if constexpr (!GRAMQ) *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
                 mwr[ch] = maskg[i0 >> 5];
             }
         }
@@ -82,6 +88,24 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
         if (k < K) xk[u] = x[gk[u]];
+    }
+    if constexpr (GRAMQ && NCH > 0) {
+        if (tid < kb) { s_gq[tid] = gk[0]; s_dq[tid] = dk[0]; }   // kb <= GRAM_KMAX <= THREADS (checked by the host)
+        __syncthreads();
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+            const int i0 = (ch * THREADS + tid) * V;
+#pragma unroll
+            for (int e = 0; e < V; ++e) qv[ch][e] = T(0);
+            if (i0 < a.ldc)
+                for (int k = 0; k < K; ++k) {
+                    T gv[V];
+                    *reinterpret_cast<int4*>(gv) = __ldg(reinterpret_cast<const int4*>(a.G + (size_t)s_gq[k] * a.ldg + i0));
+                    const T d = s_dq[k];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) qv[ch][e] += gv[e] * d;
+                }
+        }
     }
 
     // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index.
@@ -361,6 +385,7 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
     __syncwarp();
 
     // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs
+    if (a.skip_rhs) return;   // the next iteration forms q from the Gram matrix: no right-hand side needed
     void *pn, *pl;
     rhs_rows(a, row, pn, pl);
     float scale = 1.f;
