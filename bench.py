@@ -42,8 +42,8 @@ CONFIGS = {
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default 20; 3 for the IRLS config and the reference arm)")
+    ap.add_argument("--warmup", type=int, default=None, help="untimed warm-up steps (default 5; 3 for IRLS / reference)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=None, help="signals per GPU per step (default: the config's)")
@@ -51,8 +51,15 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=None, help="signals in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-kernel-timing", action="store_true", help="no per-kernel CUDA events in the timed region (roofline absent)")
     ap.add_argument("--gather-x", action="store_true", help="also gather the dense coefficients to rank 0 each step")
-    return ap.parse_args()
+    args = ap.parse_args()
+    slow = args.impl == "reference" or CONFIGS[args.config].get("solver") == "irls"
+    if args.steps is None:
+        args.steps = 3 if slow else 20
+    if args.warmup is None:
+        args.warmup = 3 if slow else 5
+    return args
 
 
 def make_workload(cfg, batch, seed):
@@ -147,6 +154,16 @@ def measured_peaks():
     if os.path.exists(p):
         return json.load(open(p)), "measured"
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def ncu_traffic():
+    """DRAM bytes per full-batch launch (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/ncu_traffic.json, written by tools/ncu_summary.py --traffic)."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return {}
+    with open(p) as f:
+        return json.load(f).get("bytes_per_launch", {})
 
 
 def run_reference(args, cfg):
@@ -319,20 +336,36 @@ def run_b200(args, cfg):
         sampler.start()
     for _ in range(args.warmup):
         step_dev()
+    # ---- the timed region: K steps, no per-kernel events inside (they cost ~2 ms per step: every record drains the
+    # launch pipeline); one event per step boundary only, for the per-step spread
     solver.reset_counters()
-    solver.set_timing(True)
+    solver.set_timing(False)
     barrier()
     t_wall0 = time.perf_counter()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    marks[0].record()
+    for i in range(args.steps):
         step_dev()
-    e1.record()
+        marks[i + 1].record()
     barrier()
     if rank == 0:
         sampler.window(t_wall0, time.perf_counter())
+    ms = marks[0].elapsed_time(marks[-1])
+    step_ms = [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)]
+    launches_timed = solver.counters()["launches"]
+    # ---- the same K steps again with every launch of the lockstep loop bracketed by CUDA events on its stream: the
+    # per-kernel durations behind `roofline` / `kernels` (shares are taken against this instrumented pass's own time)
+    solver.reset_counters()
+    solver.set_timing(not args.no_kernel_timing)
+    barrier()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    for _ in range(args.steps):
+        step_dev()
+    p1.record()
+    barrier()
+    ms_prof = p0.elapsed_time(p1)
     clocks = sampler.stop() if rank == 0 else None
-    ms = e0.elapsed_time(e1)
     solver.set_timing(False)
     counters, timing = solver.counters(), solver.timing()
     iters_mean = float(dIt.to(torch.float64).mean().item())
@@ -387,8 +420,41 @@ def run_b200(args, cfg):
                 "peak_source": f"{peak_src} bf16_tflops_sustained / " + ("6 (TF32 = bf16/2, 3 MMAs per fp32 product)" if tf32 else
                                "3 (3 fp16-rate MMAs per fp32 product)"),
                 "launches": counters["contractions"], "avg_launch_ms": timing["contraction_ms"] / max(1, counters["contractions"]),
-                "share_of_step": timing["contraction_ms"] / ms, "step_kernel_share": timing["step_ms"] / ms,
+                "share_of_step": timing["contraction_ms"] / ms_prof, "step_kernel_share": timing["step_ms"] / ms_prof,
                 "path": ("tcgen05 3-split, tf32 containers" if tf32 else "tcgen05 3-split, fp16 containers") if tensor_path else "simt fp32"}
+    # every kernel class of the lockstep loop against its own bound (the scan kernels are HBM-streaming: c read + written,
+    # q read when it comes from the contraction; algorithmic bytes per signal-iteration = 3 (or 2) x Npad x sizeof(T))
+    prof = solver.kernel_profile()
+    npad = -(-N // 128) * 128
+    isz_k = dt.itemsize
+    hbm_peak = peaks["hbm_gbs"]
+    traffic = ncu_traffic()
+
+    def hbm_entry(name, ms_k, rows_k, bytes_k, launches_note):
+        if ms_k <= 0:
+            return None
+        gbs = bytes_k / (ms_k * 1e-3) / 1e9
+        return {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+                "traffic": traffic.get(name), "peak_source": f"{peak_src} hbm_gbs", "signal_rows": rows_k,
+                "share_of_step": ms_k / ms_prof, "algorithmic_bytes": launches_note}
+    k_stream = hbm_entry("homotopy_scan_kernel (Q streamed)", prof["scan_stream"]["ms"], prof["scan_stream"]["rows"],
+                         3.0 * npad * isz_k * prof["scan_stream"]["rows"], "3 x Npad x sizeof(T) per signal-iteration: c read, q read, c written")
+    k_gram = hbm_entry("homotopy_scan_kernel (q from Gram rows)", prof["scan_gram"]["ms"], prof["scan_gram"]["rows"],
+                       2.0 * npad * isz_k * prof["scan_gram"]["rows"], "2 x Npad x sizeof(T) per signal-iteration: c read, c written; "
+                       "K rows of G per signal come from L2 (L2-bound, see DESIGN.md)")
+    scan_ms = prof["scan_stream"]["ms"] + prof["scan_gram"]["ms"]
+    k_scan = hbm_entry("homotopy_scan_kernel (both variants)", scan_ms, prof["scan_stream"]["rows"] + prof["scan_gram"]["rows"],
+                       npad * isz_k * (3.0 * prof["scan_stream"]["rows"] + 2.0 * prof["scan_gram"]["rows"]),
+                       "sum of the two variants")
+    k_alg = {"kernel": "homotopy_algebra_kernel", "bound": "l2 / latency (K x K inverse update per warp, K-atom gather from L2)",
+             "signal_rows": prof["algebra"]["rows"], "share_of_step": prof["algebra"]["ms"] / ms_prof,
+             "us_per_1k_rows": 1e6 * prof["algebra"]["ms"] / max(1, prof["algebra"]["rows"]),
+             "traffic": traffic.get("homotopy_algebra_kernel")} if prof["algebra"]["ms"] > 0 else None
+    roofline["traffic"] = traffic.get("contract_x3_pair_kernel")
+    kernels = [k for k in (roofline, k_scan, k_stream, k_gram, k_alg) if k]
+    # `roofline` names the kernel with the largest measured share of the step
+    if k_scan and k_scan["share_of_step"] > roofline["share_of_step"]:
+        roofline = dict(k_scan)
     whole = {"achieved": 2.0 * M * N * world * batch * args.steps * (iters_mean + 1) / (ms * 1e-3) / 1e12,
              "unit": "TFLOP/s", "note": "whole-solve algorithmic flops 2*M*N*(iters+1) per signal / step time"}
     whole["frac"] = whole["achieved"] / (peak * world)
@@ -413,7 +479,12 @@ def run_b200(args, cfg):
                    "batch_per_gpu": batch, "mean_iters": iters_mean, "converged_frac": converged,
                    "l2": "working set (C,Q,X: 3 x %.0f MB per GPU) exceeds the 126 MB L2; no explicit flush" % (batch * N * dt.itemsize / 1e6),
                    "contraction_path": args.path, "gather_x": bool(args.gather_x)},
-        "e2e": e2e, "gpu_launches": counters["launches"], "roofline": roofline, "whole_solve": whole,
+        "e2e": e2e, "gpu_launches": launches_timed, "roofline": roofline, "kernels": kernels, "whole_solve": whole,
+        "step_ms": {"median": float(np.median(step_ms)), "min": min(step_ms), "max": max(step_ms),
+                    "note": "per-step device time inside the timed region (rank 0); `value` uses the whole region"},
+        "kernel_timing": {"ms_per_step_instrumented": ms_prof / args.steps,
+                          "note": "per-kernel CUDA events are recorded in a second pass of the same K steps right after the "
+                                  "timed region; shares are fractions of that pass"},
         "cpu_baseline": cpu, "clocks": clocks,
     }
     print(json.dumps(line))

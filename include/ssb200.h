@@ -156,6 +156,10 @@ int ssb200_reset_counters(void* handle);
 int ssb200_get_counters(void* handle, uint64_t counters[4]);
 int ssb200_set_timing(void* handle, int enabled);
 int ssb200_get_timing(void* handle, double ms[2]);
+/* per-kernel-class profile of the homotopy lockstep loop (timing enabled): summed device time and the signal-rows processed
+ *   class 0 contraction, 1 all step kernels, 2 scan kernel with Q streamed from HBM, 3 scan kernel with q formed from the
+ *   Gram matrix, 4 algebra kernel, 5 monolithic step / init kernels */
+int ssb200_get_kernel_profile(void* handle, double ms[6], uint64_t rows[6]);
 int ssb200_set_contraction_path(void* handle, int path);
 /* test / bench hook for the contraction kernel alone: Q[r][n] = sum_m A[m][n] * P[r][m] for `rows` host rows
  * (P: rows x M, Q: rows x N, both dense row-major), computed by path 1 (SIMT) or 2 (tcgen05, float32);

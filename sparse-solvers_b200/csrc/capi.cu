@@ -255,7 +255,7 @@ void ssb200_destroy(void* handle)
 
 int ssb200_reset_counters(void* h)
 { return guarded([&] { SSB_REQUIRE(h, "null handle"); auto* b = static_cast<SolverBase*>(h);
-                       for (auto& c : b->counters) c = 0; b->ms[0] = b->ms[1] = 0.0; }); }
+                       for (auto& c : b->counters) c = 0; for (auto& m : b->ms) m = 0.0; for (auto& r : b->kernel_rows) r = 0; }); }
 int ssb200_get_counters(void* h, uint64_t counters[4])
 { return guarded([&] { SSB_REQUIRE(h && counters, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        for (int i = 0; i < 4; ++i) counters[i] = b->counters[i]; }); }
@@ -263,6 +263,9 @@ int ssb200_set_timing(void* h, int enabled)
 { return guarded([&] { SSB_REQUIRE(h, "null handle"); static_cast<SolverBase*>(h)->timing = enabled != 0; }); }
 int ssb200_get_timing(void* h, double ms[2])
 { return guarded([&] { SSB_REQUIRE(h && ms, "null pointer"); auto* b = static_cast<SolverBase*>(h); ms[0] = b->ms[0]; ms[1] = b->ms[1]; }); }
+int ssb200_get_kernel_profile(void* h, double ms[6], uint64_t rows[6])
+{ return guarded([&] { SSB_REQUIRE(h && ms && rows, "null pointer"); auto* b = static_cast<SolverBase*>(h);
+                       for (int i = 0; i < SolverBase::NCLS; ++i) { ms[i] = b->ms[i]; rows[i] = b->kernel_rows[i]; } }); }
 int ssb200_set_contraction_path(void* h, int path)
 { return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 3, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
 

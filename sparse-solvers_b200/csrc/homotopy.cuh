@@ -147,6 +147,7 @@ private:
         int ws_kmax = 0;
         // instrumentation, merged into the handle after the solve
         uint64_t counters[4] = { 0, 0, 0, 0 };
+        uint64_t rows[6] = { 0, 0, 0, 0, 0, 0 };   // signal-rows per launch class (SolverBase::kernel_rows)
         struct span { cudaEvent_t a, b; int cls; };
         std::vector<span> spans;
         std::vector<cudaEvent_t> pool;

@@ -284,7 +284,8 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     // 4-byte copy can wait milliseconds, and on the main stream that wait would stall the kernels behind it.  It reads the counts back asynchronously, sizes the grids from the newest one
     // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
     // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
-    constexpr uint32_t RUN_AHEAD = 8;
+    uint32_t RUN_AHEAD = 8;
+    if (const char* e = getenv("SSB200_RUN_AHEAD")) RUN_AHEAD = (uint32_t)std::max(1, std::min(64, atoi(e)));   // tuning knob
     uint32_t gram_iters = 16;                                    // iterations 1 .. gram_iters - 1 take q from the Gram matrix
     if (const char* e = getenv("SSB200_GRAM_ITERS")) gram_iters = (uint32_t)std::max(0, std::min(32, atoi(e)));   // tuning knob
     if (!split_ok || nch == 0 || algebra_warps(homotopy_algebra_slice<T>((int)gram_iters, ((int)gram_iters + 1) | 1)) == 0) gram_iters = 0;
@@ -305,6 +306,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     size_t known = rows;         // newest count the host has seen (upper bound of the current one)
     uint32_t seen = 0;           // ... which is counts[seen]
     uint32_t last = 0;
+    std::vector<uint8_t> route((size_t)max_iter + 2, 0);   // launch class of every iteration's scan (kernel profile)
     for (uint32_t it = 1; it <= max_iter; ++it) {
         const uint32_t must = async ? (it > RUN_AHEAD ? it - RUN_AHEAD : 0) : it - 1;   // counts[must] has to be in
         for (uint32_t j = seen + 1; j < it; ++j) {
@@ -339,12 +341,20 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const int aw = (gram || a.skip_rhs) ? 4 : (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
         if (aw > 0) {
+            const int sp_scan = L.begin(timing, gram ? 3 : 2);
             launch_scan(threads, nch, gram, (unsigned)known, st, a, kb);
+            L.end(sp_scan);
+            const int sp_alg = L.begin(timing, 4);
             launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
+            L.end(sp_alg);
             L.counters[0] += 2;
+            route[it] = gram ? 3 : 2;
         } else {
+            const int sp_step = L.begin(timing, 5);
             launch_step(threads, nch, gs, (unsigned)known, smem, st, a, kb, ks);
+            L.end(sp_step);
             L.counters[0]++;
+            route[it] = 5;
         }
         L.end(span);
         L.counters[3]++;
@@ -357,6 +367,12 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     SSB_CUDA(cudaStreamSynchronize(st));
     SSB_CUDA(cudaStreamSynchronize(L.side));
     for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
+    for (uint32_t it = 1; it <= last; ++it) {
+        const uint64_t n = (uint64_t)h_counts[it - 1];           // signals that entered iteration `it`
+        L.rows[route[it]] += n;
+        if (route[it] != 5) L.rows[4] += (uint64_t)h_counts[it]; // the algebra kernel runs for those that continue
+        L.rows[1] += n;
+    }
 }
 
 // folds a lane's counters and event-timed spans into the handle (stream already synchronised)
@@ -365,6 +381,7 @@ void Homotopy<T>::merge(Lane& L)
 {
     std::lock_guard<std::mutex> g(merge_mu_);
     for (int i = 0; i < 4; ++i) { counters[i] += L.counters[i]; L.counters[i] = 0; }
+    for (int i = 0; i < NCLS; ++i) { kernel_rows[i] += L.rows[i]; L.rows[i] = 0; }
     for (auto& s : L.spans) {
         float t = 0.f;
         if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) ms[s.cls] += t;

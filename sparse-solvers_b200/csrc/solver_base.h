@@ -21,7 +21,11 @@ struct SolverBase {
     cudaStream_t stream = nullptr;       // the handle's own stream (host-pointer entry points)
     uint64_t counters[4] = { 0, 0, 0, 0 };
     bool timing = false;
-    double ms[2] = { 0.0, 0.0 };
+    // event-timed launch classes: 0 contraction, 1 all step kernels, 2 scan (Q streamed), 3 scan (q from the Gram matrix),
+    // 4 algebra, 5 monolithic step / init; kernel_rows[cls] = signal-rows those launches processed
+    static constexpr int NCLS = 6;
+    double ms[NCLS] = { 0.0, 0.0, 0.0, 0.0, 0.0, 0.0 };
+    uint64_t kernel_rows[NCLS] = { 0, 0, 0, 0, 0, 0 };
     int contraction_path = 0;            // 0 auto, 1 SIMT, 2 tcgen05 (fp16 containers), 3 tcgen05 with tf32 containers
 
     // pairs of events bracketing launches of class `cls` on the current solve's stream

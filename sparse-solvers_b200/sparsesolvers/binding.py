@@ -106,6 +106,14 @@ class _Solver:
         check(lib().ssb200_get_timing(self._h, ms))
         return dict(contraction_ms=ms[0], step_ms=ms[1])
 
+    KERNEL_CLASSES = ("contraction", "step_all", "scan_stream", "scan_gram", "algebra", "step_mono")
+
+    def kernel_profile(self):
+        """Per kernel class of the lockstep loop: summed device ms (timing enabled) and signal-rows processed."""
+        ms, rows = (C.c_double * 6)(), (C.c_uint64 * 6)()
+        check(lib().ssb200_get_kernel_profile(self._h, ms, rows))
+        return {k: dict(ms=ms[i], rows=int(rows[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+
     def set_contraction_path(self, path):
         check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path])))
 
