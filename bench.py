@@ -36,6 +36,8 @@ CONFIGS = {
     # BASELINE says 1024x4096; the reference's IRLS is undefined for M < N: the tall reading is the oracle-able one
     "C4": dict(m=4096, n=1024, k=64, dtype="float64", batch=16384, tol=1e-3, max_iter=50, solver="irls"),
     "C5": dict(m=4096, n=16384, k=128, dtype="float32", batch=8192, tol=1e-3, max_iter=272),
+    # the reference's own benchmark grid (src/solvers/homotopy_bench.cpp:57-60), SURVEY.md §8(f) N2
+    "GRID": dict(m=512, n=2048, k=0, dtype="float32", batch=32, tol=0.1, max_iter=2048, solver="grid"),
 }
 
 
@@ -226,6 +228,78 @@ def run_irls(args, cfg):
                          "unit": "TFLOP/s", "frac": flops / secs / 1e12 / 40.0, "traffic": None,
                          "peak_source": "B200 FP64 datasheet (no measured FP64 figure in MEASURED_PEAKS.json); separately rounded mul/add cannot use FMA: half of it is the ceiling"},
             "cpu_baseline": None}
+    print(json.dumps(line))
+
+
+def grid_workload(M, N, seed=0):
+    """The reference bench's inputs (src/solvers/homotopy_bench.cpp:14-48): haystack ~ N(0.5, 0.1) M x N, signal ~ N(0.5, 0.1)
+    with +1 on every second entry; before solve i the same +1 pattern is added to column i % N and taken away after."""
+    rng = np.random.default_rng(seed)
+    hay = (0.5 + 0.1 * rng.standard_normal((M, N))).astype(np.float32)
+    sig = (0.5 + 0.1 * rng.standard_normal(M)).astype(np.float32)
+    sig[::2] += 1.0
+    return hay, sig
+
+
+def run_grid(args, cfg):
+    """The reference's own benchmark grid (homotopy_bench.cpp:57-60: M 16..512 x N 16..2048, multiplier 4, tolerance 0.1,
+    max_iter = N), re-hosted without Google Benchmark: per cell, `solves` single-signal solves with the dictionary edited in
+    place between them (the handle follows the edit through ssb200_homotopy_refresh), GPU next to the reference on one
+    host thread.  One JSON line; `value` = solves per second over the whole grid."""
+    import torch
+    import sparsesolvers as ss
+    from oracle import ref
+    Ms, Ns = (16, 64, 256, 512), (16, 64, 256, 1024, 2048)
+    solves = args.batch or 32
+    cells, total_gpu, total_n = [], 0.0, 0
+    have_ref = (not args.no_cpu_baseline) and ref.available()
+    if have_ref:
+        ref.set_blas_threads(1)
+    for M in Ms:
+        for N in Ns:
+            hay, sig = grid_workload(M, N)
+            solver = ss.Homotopy(hay)
+            it_gpu, it_ref = np.zeros(solves, dtype=np.int64), np.zeros(solves, dtype=np.int64)
+            for rep in range(2):                       # first pass warms the handle up
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for i in range(solves):
+                    n = i % N
+                    hay[::2, n] += 1.0
+                    solver.refresh(hay)
+                    x, r = solver.solve(sig, 0.1, N)
+                    it_gpu[i] = r.iter
+                    hay[::2, n] -= 1.0
+                gpu_s = time.perf_counter() - t0
+            cell = {"m": M, "n": N, "gpu_ms_per_solve": 1e3 * gpu_s / solves, "gpu_mean_iters": float(it_gpu.mean())}
+            if have_ref:
+                t0 = time.perf_counter()
+                done = 0
+                for i in range(solves):                 # bounded: the largest cells take ~20 s per solve on one core
+                    n = i % N
+                    hay[::2, n] += 1.0
+                    xr, itr, er = ref.homotopy(hay, sig[None, :], 0.1, N, threads=1)
+                    it_ref[i] = itr[0]
+                    hay[::2, n] -= 1.0
+                    done += 1
+                    if time.perf_counter() - t0 > 8.0:
+                        break
+                cpu_s = time.perf_counter() - t0
+                cell.update(cpu_ms_per_solve=1e3 * cpu_s / done, cpu_solves=done, cpu_mean_iters=float(it_ref[:done].mean()),
+                            gpu_mean_iters_same_solves=float(it_gpu[:done].mean()),
+                            iters_equal=int((it_ref[:done] == it_gpu[:done]).sum()),
+                            gpu_hit_max_iter=int((it_gpu == N).sum()), cpu_hit_max_iter=int((it_ref[:done] == N).sum()))
+            cells.append(cell)
+            total_gpu += gpu_s
+            total_n += solves
+            del solver
+    line = {"metric": "homotopy solves/sec over the reference bench grid", "value": total_n / total_gpu, "unit": "solves/s", "n_gpus": 1,
+            "steps": 1, "warmup": 1, "ms_per_step": 1e3 * total_gpu, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"GRID: homotopy_bench.cpp grid, M {Ms} x N {Ns}, tol 0.1, max_iter N, {solves} solves per cell, "
+                                   "dictionary edited in place and refreshed before every solve"},
+            "cells": cells, "cpu_baseline": {"kind": "reference", "cores": 1, "unit": "ms per solve, per cell (cells[].cpu_ms_per_solve)",
+                                             "sample": f"{solves} solves per cell"} if have_ref else None}
     print(json.dumps(line))
 
 
@@ -501,6 +575,8 @@ def main():
         run_irls(args, cfg)
     elif cfg.get("solver") == "single":
         run_single(args, cfg)
+    elif cfg.get("solver") == "grid":
+        run_grid(args, cfg)
     else:
         run_b200(args, cfg)
 

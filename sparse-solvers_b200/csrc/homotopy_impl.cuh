@@ -142,21 +142,31 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* 
 }
 
 
-template <typename T, int THREADS, int NCH, bool GS>
+constexpr int STEP_KR = 3, STEP_KR_BIG = 16;   // active-set slots per thread of the step kernel: K <= KR * threads
+
+template <typename T, int THREADS, int NCH, bool GS, int KR = STEP_KR>
 static void launch_step_variant(unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
     static size_t configured = 0;   // per process; one device per process in every supported deployment
     if (smem > 48 * 1024 && smem > configured) {
-        SSB_CUDA(cudaFuncSetAttribute(homotopy_step_kernel<T, THREADS, NCH, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        SSB_CUDA(cudaFuncSetAttribute(homotopy_step_kernel<T, THREADS, NCH, GS, KR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         configured = 200 * 1024;
     }
-    homotopy_step_kernel<T, THREADS, NCH, GS><<<grid, THREADS, smem, st>>>(a, kb, ks);
+    homotopy_step_kernel<T, THREADS, NCH, GS, KR><<<grid, THREADS, smem, st>>>(a, kb, ks);
     SSB_CUDA(cudaGetLastError());
 }
 
 template <typename T>
 static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
+    // active sets beyond 3 slots per thread (max_iterations > 767): 256 threads, 16 slots each, inverse worked on in HBM
+#define SSB_STEP_BIG(NC)                                                                          \
+    if (a.Kmax > STEP_KR * threads && threads == 256 && nch == NC) {                              \
+        launch_step_variant<T, 256, NC, false, STEP_KR_BIG>(grid, smem, st, a, kb, ks);           \
+        return;                                                                                   \
+    }
+    SSB_STEP_BIG(1) SSB_STEP_BIG(2) SSB_STEP_BIG(4) SSB_STEP_BIG(0)
+#undef SSB_STEP_BIG
 #define SSB_STEP(TH, NC)                                                                          \
     if (threads == TH && nch == NC) {                                                             \
         if (gs) launch_step_variant<T, TH, NC, true>(grid, smem, st, a, kb, ks);                  \
@@ -271,9 +281,10 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     const int chunks128 = (Npad + 128 * V - 1) / (128 * V), chunks256 = (Npad + 256 * V - 1) / (256 * V);
     int threads = chunks128 <= 4 ? 128 : 256;
     int nch = chunks128 <= 1 ? 1 : chunks128 <= 2 ? 2 : chunks128 <= 4 ? 4 : chunks256 <= 4 ? 4 : 0;
-    if (const char* e = getenv("SSB200_STEP_THREADS")) if (atoi(e) == 256) {                          // tuning knob
-        threads = 256; nch = chunks256 <= 1 ? 1 : chunks256 <= 2 ? 2 : chunks256 <= 4 ? 4 : 0;
-    }
+    bool wide = L.ws_kmax > STEP_KR * 128;            // more active-set slots than 128 threads hold: 256 threads
+    if (const char* e = getenv("SSB200_STEP_THREADS")) if (atoi(e) == 256) wide = true;               // tuning knob
+    if (wide) { threads = 256; nch = chunks256 <= 1 ? 1 : chunks256 <= 2 ? 2 : chunks256 <= 4 ? 4 : 0; }
+    const bool big = L.ws_kmax > STEP_KR * threads;   // ... than 256 threads hold at 3 each: the 16-slot variant
     const size_t g_budget = 96 * 1024;
     bool split_ok = true;                                                                            // scan + algebra kernels
     if (const char* e = getenv("SSB200_SPLIT")) split_ok = atoi(e) != 0;                              // tuning knob
@@ -284,6 +295,8 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     // 4-byte copy can wait milliseconds, and on the main stream that wait would stall the kernels behind it.  It reads the counts back asynchronously, sizes the grids from the newest one
     // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
     // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
+    int sync_iters = 0;
+    if (const char* e = getenv("SSB200_SYNC_ITERS")) sync_iters = atoi(e);                            // debugging aid
     uint32_t RUN_AHEAD = 8;
     if (const char* e = getenv("SSB200_RUN_AHEAD")) RUN_AHEAD = (uint32_t)std::max(1, std::min(64, atoi(e)));   // tuning knob
     uint32_t gram_iters = 16;                                    // iterations 1 .. gram_iters - 1 take q from the Gram matrix
@@ -333,10 +346,10 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         a.it = it;
         const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
         const int ks = (kb + 1) | 1;                                          // odd row stride: conflict-free column reads
-        const bool gs = (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
+        const bool gs = !big && (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
         const size_t smem = homotopy_step_smem<T>(L.ws_kmax, Npad, gs ? kb + 1 : 0, ks);
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
-        SSB_REQUIRE(L.ws_kmax <= 3 * threads, "max_iterations too large for the step kernel's per-slot registers");
+        SSB_REQUIRE(L.ws_kmax <= STEP_KR_BIG * 256, "max_iterations too large: the active set is limited to 4096 atoms");
         const size_t slice = homotopy_algebra_slice<T>(kb, ks);
         const int aw = (gram || a.skip_rhs) ? 4 : (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
@@ -357,6 +370,16 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
             route[it] = 5;
         }
         L.end(span);
+        if (sync_iters) {   // debugging aid: find the iteration a device fault belongs to
+            int hk = -1;
+            T hl = T(0);
+            uint32_t hp = 0;
+            const cudaError_t e = cudaStreamSynchronize(st);
+            if (e == cudaSuccess) { cudaMemcpy(&hk, a.Kcur, sizeof(int), cudaMemcpyDeviceToHost); cudaMemcpy(&hl, a.lam, sizeof(T), cudaMemcpyDeviceToHost);
+                                    cudaMemcpy(&hp, a.gam + (hk > 0 ? hk - 1 : 0), sizeof(uint32_t), cudaMemcpyDeviceToHost); }
+            if (e != cudaSuccess || sync_iters > 1) fprintf(stderr, "[ssb200] it %u known %zu kb %d K[0] %d lam[0] %.9g lastslot %u big %d gs %d aw %d: %s\n", it, known, kb, hk, (double)hl, hp, (int)big, (int)gs, aw, cudaGetErrorString(e));
+            SSB_CUDA(e);
+        }
         L.counters[3]++;
         SSB_CUDA(cudaEventRecord(L.iter_events[it % (RUN_AHEAD + 1)], st));
         SSB_CUDA(cudaStreamWaitEvent(L.side, L.iter_events[it % (RUN_AHEAD + 1)], 0));

@@ -284,7 +284,8 @@ __device__ __forceinline__ void matvec(const T* G, int ld, int K, const T* v, T*
 // memory -- and c / q are read from HBM exactly once per iteration.
 //   NCH  chunks of c,q a thread keeps in registers; 0 = dictionary too wide, c and q are re-read for the update
 //   GS   inverse held in shared memory (row stride ks) for the iteration; false = worked on in place in HBM
-template <typename T, int THREADS, int NCH, bool GS>
+//   KR   active-set slots a thread keeps in registers: K <= KR * THREADS (3 by default; 16 for active sets up to 4096)
+template <typename T, int THREADS, int NCH, bool GS, int KR = 3>
 __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, int kb, int ks)
 {
     constexpr int V = 16 / sizeof(T);
@@ -375,8 +376,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     __syncthreads();
     // per-slot values stay in registers (slot k lives in thread k % THREADS) so that no load is waited for
     // before its value is needed: x at the active atoms, the Gram row of a joining atom, c at the active atoms
-    constexpr int KR = 3;   // K <= KR * THREADS (checked by the host)
-    T xk[KR], u1r[KR], cgr[KR];
+    T xk[KR], u1r[KR], cgr[KR];   // K <= KR * THREADS (checked by the host)
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
@@ -550,9 +550,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         uu = warp_sum(uu);
         const T dd = T(1) / (dot - uu);                                                       // :228
         {                                                                                     // inv += d u2 u2^T
+            // row = e / K by multiply-high, exact while e * K < 2^32, i.e. K < 1625; a plain division beyond
             const uint32_t total = (uint32_t)(K * K), magic = (uint32_t)((0x100000000ull + K - 1) / K);
+            const bool mulhi_exact = K < 1600;
             for (uint32_t e = tid; e < total; e += THREADS) {
-                const uint32_t r = __umulhi(e, magic), k = e - r * K;
+                const uint32_t r = mulhi_exact ? __umulhi(e, magic) : e / (uint32_t)K, k = e - r * K;
                 Gm[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
             }
         }

@@ -290,3 +290,69 @@ def test_c5_large_dictionary_shape(ss):
     r = parity.compare(X, it, err, Xr, itr, er, c0_inf(A, Y))
     print(parity.assert_parity(r, np.float32, "C5", noise_rate=0.1), it.min(), it.max())
     assert ((parity.support(X, 1e-5) == (X0 != 0)).all(axis=1)).mean() > 0.9
+
+
+@pytest.mark.parametrize("dtype,max_iter", [(np.float32, 500), (np.float32, 1023), (np.float64, 1023)])
+def test_large_max_iterations(ss, dtype, max_iter):
+    """The reference takes any max_iterations (its bench passes N, homotopy_bench.cpp:41).  The active-set capacity is
+    min(max_iterations + 1, N): above 384 slots the step kernel runs 256 threads, above 768 the 16-slots-per-thread
+    variant with the inverse worked on in HBM.  Converging signals must come out as the oracle has them."""
+    from oracle import port
+    from sparsesolvers import synth
+    A = synth.dictionary(128, 1024, dtype=dtype, seed=77)
+    Y, _ = synth.sparse_signals(A, 48, 8, seed=78)
+    Xr, itr, er = port.homotopy(A, Y, 1e-3, max_iter)
+    assert itr.max() < 40
+    s = ss.Homotopy(A)
+    stats, _ = check_homotopy(s, A, Y, 1e-3, max_iter, Xr, itr, er, f"{np.dtype(dtype).name} max_iter={max_iter}")
+    x, rep = s.solve(Y[0], 1e-3, max_iter)              # single-signal entry with the same capacity
+    assert rep.iter == itr[0]
+    np.testing.assert_allclose(x, Xr[0], rtol=0, atol=1e-4 * np.abs(Xr[0]).max())
+
+
+def test_long_runs_large_active_set(ss):
+    """Signals the reference walks to max_iterations (sign quirk, homotopy-cpu.cpp:223-224) with a large budget: 900
+    iterations on the 16-slot variant.  The trajectory is chaotic at that length, so the check is the report the
+    reference gives (iter == max_iterations for the same signals, finite coefficients), not the digits."""
+    from oracle import port
+    from sparsesolvers import synth
+    A = synth.dictionary(96, 1024, dtype=np.float32, seed=81)
+    Y, _ = synth.sparse_signals(A, 24, 6, seed=82, normalise_sign=False)
+    Xr, itr, er = port.homotopy(A, Y, 1e-3, 900)
+    X, it, err = ss.Homotopy(A).solve_batch(Y, 1e-3, 900)
+    assert np.isfinite(X).all()
+    long_ref, short_ref = itr == 900, itr <= 10
+    assert long_ref.any() and short_ref.any()
+    # converging signals agree exactly; of those the reference walks to the budget, most must do so here as well
+    assert (it[short_ref] == itr[short_ref]).all()
+    assert (it[long_ref] == 900).sum() * 2 >= long_ref.sum(), (it[long_ref], itr[long_ref])
+    assert (it[~short_ref] > 10).all()
+
+
+@pytest.mark.parametrize("M,N", [(16, 16), (16, 64), (64, 64), (64, 256)])
+def test_reference_bench_grid_cells(ss, M, N):
+    """The reference's own benchmark workload (src/solvers/homotopy_bench.cpp:14-48; bench.py --config GRID): a +1 pattern
+    planted in column n of a N(0.5, 0.1) haystack, edited IN PLACE between solves (the handle follows through refresh),
+    tolerance 0.1, max_iterations = N.  The needle must come out on top and the solve must converge; iteration counts
+    are compared with the oracle (the two CPU builds themselves differ by a few iterations on this ill-conditioned
+    dictionary, so equality is required of the short runs only)."""
+    import bench
+    from oracle import port
+    hay, sig = bench.grid_workload(M, N)
+    s = ss.Homotopy(hay)
+    same = 0
+    solves = 8
+    for i in range(solves):
+        n = i % N
+        hay[::2, n] += 1.0
+        s.refresh(hay)
+        x, rep = s.solve(sig, 0.1, N)
+        xr, itr, er = port.homotopy(hay, sig[None, :], 0.1, N)
+        hay[::2, n] -= 1.0
+        assert int(np.argmax(np.abs(x))) == n == int(np.argmax(np.abs(xr[0])))
+        assert rep.solution_error <= 0.1 or rep.iter == N
+        same += int(rep.iter == itr[0])
+        if itr[0] <= 8:
+            assert rep.iter == itr[0]
+            np.testing.assert_allclose(x, xr[0], rtol=0, atol=1e-3 * np.abs(xr[0]).max())
+    assert same >= solves // 2, f"{same}/{solves} iteration counts equal to the oracle's"
