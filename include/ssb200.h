@@ -137,6 +137,17 @@ void ssb200_destroy(void* handle);
  */
 int ssb200_reconstruct_batch_f32(void* homotopy_handle, const float* X, size_t batch, size_t ldx, float* Y, size_t ldy);
 int ssb200_reconstruct_batch_f64(void* homotopy_handle, const double* X, size_t batch, size_t ldx, double* Y, size_t ldy);
+/* the same with DEVICE pointers (dX: batch x N with leading dimension ldx, dY: batch x M), enqueued on `stream` and synchronised */
+int ssb200_reconstruct_batch_dev_f32(void* homotopy_handle, const float* dX, size_t batch, size_t ldx, float* dY, size_t ldy, void* stream);
+int ssb200_reconstruct_batch_dev_f64(void* homotopy_handle, const double* dX, size_t batch, size_t ldx, double* dY, size_t ldy, void* stream);
+/* sparse form of a dense result (new): for every row of dX its non-zero entries in index order as
+ * (d_idx[b*cap + k], d_val[b*cap + k]), k < min(d_count[b], cap); unused slots hold (-1, 0).  d_count[b] is the number of
+ * non-zeros found and may exceed cap (the row was cut).  A homotopy solution has at most min(max_iterations + 1, N)
+ * non-zeros, so cap = that bound never cuts.  All pointers are DEVICE pointers on `device`. */
+int ssb200_compress_rows_dev_f32(const float* dX, size_t batch, size_t n, size_t ldx, size_t cap, int32_t* d_idx, float* d_val,
+                                 int32_t* d_count, int device, void* stream);
+int ssb200_compress_rows_dev_f64(const double* dX, size_t batch, size_t n, size_t ldx, size_t cap, int32_t* d_idx, double* d_val,
+                                 int32_t* d_count, int device, void* stream);
 int ssb200_norm_l1_f32(float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
 int ssb200_norm_l1_f64(double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
 

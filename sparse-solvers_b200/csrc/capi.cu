@@ -214,6 +214,18 @@ int ssb200_homotopy_solve_batch_dev_##SFX(void* h, const T* Y, size_t batch, siz
 int ssb200_reconstruct_batch_##SFX(void* h, const T* X, size_t batch, size_t ldx, T* Y, size_t ldy)                     \
 { return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (X && Y), "null pointer");                \
                        device_guard g(s->device); s->reconstruct_host(X, batch, ldx, Y, ldy); }); }                     \
+int ssb200_reconstruct_batch_dev_##SFX(void* h, const T* dX, size_t batch, size_t ldx, T* dY, size_t ldy, void* stream)     \
+{ return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (dX && dY), "null pointer");               \
+                       device_guard g(s->device); s->reconstruct_dev(dX, batch, ldx, dY, ldy, (cudaStream_t)stream); }); } \
+int ssb200_compress_rows_dev_##SFX(const T* dX, size_t batch, size_t n, size_t ldx, size_t cap, int32_t* d_idx, T* d_val, \
+                                   int32_t* d_count, int device, void* stream)                                          \
+{ return guarded([&] { SSB_REQUIRE(batch == 0 || (dX && d_idx && d_val && d_count), "null pointer");                    \
+                       SSB_REQUIRE(n > 0 && cap > 0 && ldx >= n && n < ((size_t)1 << 31) && cap < ((size_t)1 << 31), "bad shape"); \
+                       require_sm100(device); device_guard g(device);                                                   \
+                       if (batch == 0) return;                                                                          \
+                       compress_rows_kernel<T><<<(unsigned)((batch + 3) / 4), 128, 0, (cudaStream_t)stream>>>(          \
+                           dX, ldx, (int)n, batch, (int)cap, d_idx, d_val, d_count);                                    \
+                       SSB_CUDA(cudaGetLastError()); SSB_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); }); }        \
 int ssb200_debug_contract_##SFX(void* h, const T* P, size_t rows, T* Q, int path, int reps, double* ms_per_launch)      \
 { return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(P && Q, "null pointer"); device_guard g(s->device);     \
                        double ms = s->debug_contract(P, rows, Q, path, reps); if (ms_per_launch) *ms_per_launch = ms; }); } \

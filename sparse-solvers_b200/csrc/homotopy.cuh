@@ -84,6 +84,31 @@ reconstruct_kernel(const T* __restrict__ At, int Mp, int M, int N, const T* __re
     }
 }
 
+// Row compaction for the sparse result form (X dense is N values per signal, its support at most
+// max_iterations + 1): one warp per signal walks its row, keeps the non-zero entries in index order as (index, value)
+// pairs, at most `cap` of them; count[b] is the number found (may exceed cap: the caller then knows the row was cut).
+template <typename T>
+__global__ void __launch_bounds__(128)
+compress_rows_kernel(const T* __restrict__ X, size_t ldx, int N, size_t batch, int cap,
+                     int* __restrict__ idx, T* __restrict__ val, int* __restrict__ count)
+{
+    const size_t b = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (b >= batch) return;
+    const int lane = threadIdx.x & 31;
+    const T* x = X + b * ldx;
+    int found = 0;
+    for (int n0 = 0; n0 < N; n0 += 32) {
+        const int n = n0 + lane;
+        const T v = n < N ? x[n] : T(0);
+        const unsigned m = __ballot_sync(0xffffffffu, v != T(0));
+        const int slot = found + __popc(m & ((1u << lane) - 1u));
+        if (v != T(0) && slot < cap) { idx[b * cap + slot] = n; val[b * cap + slot] = v; }
+        found += __popc(m);
+    }
+    for (int k = found + lane; k < cap; k += 32) { idx[b * cap + k] = -1; val[b * cap + k] = T(0); }
+    if (lane == 0) count[b] = found;
+}
+
 template <typename T>
 class Homotopy : public SolverBase {
 public:
@@ -124,6 +149,7 @@ public:
     void solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* X, size_t ldx,
                           uint32_t* iters, double* errs);
     void reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, size_t ldy);
+    void reconstruct_dev(const T* dX, size_t batch, size_t ldx, T* dY, size_t ldy, cudaStream_t st);
     // test / bench hook: Q[r][n] = sum_m A[m][n] P[r][m] through the chosen contraction kernel, `reps` launches;
     // returns the mean device time per launch in ms
     double debug_contract(const T* P, size_t rows, T* Q, int path, int reps);

@@ -653,4 +653,16 @@ void Homotopy<T>::reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, s
     SSB_CUDA(cudaStreamSynchronize(stream));
 }
 
+template <typename T>
+void Homotopy<T>::reconstruct_dev(const T* dX, size_t batch, size_t ldx, T* dY, size_t ldy, cudaStream_t st)
+{
+    SSB_REQUIRE(M > 0, "no dictionary");
+    SSB_REQUIRE(ldx >= (size_t)N && ldy >= (size_t)M, "leading dimension too small");
+    if (batch == 0) return;
+    reconstruct_kernel<T><<<(unsigned)batch, 128, 0, st>>>(At_, Mp, M, N, dX, ldx, dY, ldy);
+    SSB_CUDA(cudaGetLastError());
+    counters[0]++;
+    SSB_CUDA(cudaStreamSynchronize(st));
+}
+
 }  // namespace ssb

@@ -53,10 +53,25 @@ def _ptr(a):
     return C.c_void_p(a.ctypes.data)
 
 
+def _is_cuda(a):
+    """A torch CUDA tensor, or any other device array (CuPy, Numba, ...) exposing __cuda_array_interface__ / DLPack."""
+    if type(a).__module__.split(".")[0] == "torch":
+        return bool(getattr(a, "is_cuda", False))
+    return hasattr(a, "__cuda_array_interface__")
+
+
+def _as_torch(a):
+    import torch
+    return a if isinstance(a, torch.Tensor) else torch.from_dlpack(a) if hasattr(a, "__dlpack__") else torch.as_tensor(a, device="cuda")
+
+
 class _Solver:
     _name = None
 
     def __init__(self, A, device=0):
+        if _is_cuda(A):
+            self._init_from_cuda(_as_torch(A))
+            return
         A = np.asarray(A)
         if A.ndim != 2:
             raise ValueError("A must be 2-dimensional")
@@ -71,6 +86,34 @@ class _Solver:
         fn = getattr(lib(), f"ssb200_{self._name}_create_{self._sfx}")
         check(fn(_ptr(A), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]), C.c_ssize_t(rs), C.c_ssize_t(cs),
                  C.c_int(device), C.byref(self._h)))
+
+    def _init_from_cuda(self, A):
+        """Dictionary already on the device (a torch CUDA tensor or any DLPack / __cuda_array_interface__ producer): no host copy."""
+        import torch
+        if self._name != "homotopy":
+            raise TypeError("a device-resident dictionary is supported by Homotopy only (the IRLS set-up factorises on the host)")
+        if A.ndim != 2:
+            raise ValueError("A must be 2-dimensional")
+        dt = {torch.float32: np.dtype(np.float32), torch.float64: np.dtype(np.float64)}.get(A.dtype)
+        if dt is None:
+            raise TypeError("A must be float32 or float64")
+        self._sfx, self._ct = _SFX[dt]
+        self.dtype, self.shape, self.device = dt, tuple(A.shape), A.device.index
+        self._h = C.c_void_p()
+        fn = getattr(lib(), f"ssb200_{self._name}_create_dev_{self._sfx}")
+        check(fn(C.c_void_p(A.data_ptr()), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]), C.c_ssize_t(A.stride(0)),
+                 C.c_ssize_t(A.stride(1)), C.c_int(self.device), C.byref(self._h)))
+
+    def _check_cuda_signals(self, Y):
+        import torch
+        want = torch.float32 if self.dtype == np.float32 else torch.float64
+        if Y.dtype != want:
+            raise TypeError(f"signals must have dtype {want}")                         # py::arg().noconvert()
+        if Y.ndim != 2 or Y.shape[1] != self.shape[0]:
+            raise ValueError(f"signals must be (batch, {self.shape[0]})")
+        if Y.device.index != self.device:
+            raise ValueError(f"signals live on cuda:{Y.device.index}, the solver on cuda:{self.device}")
+        return Y if Y.stride(1) == 1 and Y.stride(0) >= Y.shape[1] else Y.contiguous()
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -131,8 +174,17 @@ class Homotopy(_Solver):
                  C.byref(it), C.byref(err)))
         return x, HomotopyReport(it.value, err.value)
 
-    def solve_batch(self, Y, tolerance=None, max_iterations=100, out=None):
-        """Y: (B, M) rows are signals.  Returns X (B, N), iters (B,) uint32, solution_errors (B,) float64."""
+    def solve_batch(self, Y, tolerance=None, max_iterations=100, out=None, sparse=False):
+        """Y: (B, M) rows are signals.  Returns X (B, N), iters (B,) uint32, solution_errors (B,) float64.
+
+        Y may also live on the device (torch CUDA tensor, or any DLPack / __cuda_array_interface__ producer): nothing is
+        copied through the host, the work is queued on torch's current stream and X, iters (int32), solution_errors come
+        back as torch tensors on that device.  With sparse=True the coefficients come back as (indices (B, cap) int32,
+        values (B, cap), counts (B,) int32) with cap = min(max_iterations + 1, N) instead of the dense X."""
+        if _is_cuda(Y):
+            return self._solve_batch_cuda(_as_torch(Y), tolerance, max_iterations, out, sparse)
+        if sparse:
+            raise ValueError("sparse=True is for device-resident signals; compress host results with numpy")
         self._check_signal(Y, 2)
         if Y.strides[1] != Y.itemsize:
             Y = np.ascontiguousarray(Y)
@@ -145,6 +197,32 @@ class Homotopy(_Solver):
         check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
                  _ptr(X), C.c_size_t(X.strides[0] // X.itemsize), _ptr(iters), _ptr(errs)))
         return X, iters, errs
+
+    def _solve_batch_cuda(self, Y, tolerance, max_iterations, out, sparse):
+        import torch
+        Y = self._check_cuda_signals(Y)
+        B, N = Y.shape[0], self.shape[1]
+        with torch.cuda.device(self.device):
+            X = out if out is not None else torch.empty((B, N), dtype=Y.dtype, device=Y.device)
+            if X.shape != (B, N) or X.dtype != Y.dtype or X.stride(1) != 1 or not X.is_cuda:
+                raise ValueError("out must be a (batch, N) CUDA tensor of the signals' dtype with unit inner stride")
+            iters = torch.empty(B, dtype=torch.int32, device=Y.device)
+            errs = torch.empty(B, dtype=torch.float64, device=Y.device)
+            stream = torch.cuda.current_stream().cuda_stream
+            if B:
+                self.solve_batch_ptr(Y.data_ptr(), B, Y.stride(0), X.data_ptr(), X.stride(0), iters.data_ptr(), errs.data_ptr(),
+                                     tolerance, max_iterations, True, stream)
+            if not sparse:
+                return X, iters, errs
+            cap = max(1, min(int(max_iterations) + 1, N))
+            idx = torch.empty((B, cap), dtype=torch.int32, device=Y.device)
+            val = torch.empty((B, cap), dtype=Y.dtype, device=Y.device)
+            cnt = torch.empty(B, dtype=torch.int32, device=Y.device)
+            check(getattr(lib(), f"ssb200_compress_rows_dev_{self._sfx}")(
+                C.c_void_p(X.data_ptr()), C.c_size_t(B), C.c_size_t(N), C.c_size_t(X.stride(0)), C.c_size_t(cap),
+                C.c_void_p(idx.data_ptr()), C.c_void_p(val.data_ptr()), C.c_void_p(cnt.data_ptr()), C.c_int(self.device),
+                C.c_void_p(stream)))
+            return (idx, val, cnt), iters, errs
 
     def solve_batch_ptr(self, y_ptr, batch, ldy, x_ptr, ldx, iters_ptr, errs_ptr, tolerance, max_iterations,
                         device_pointers, stream=0):
@@ -180,6 +258,20 @@ class Homotopy(_Solver):
 
     def reconstruct(self, X):
         """Y[b] = A X[b] on the device (ss::reconstruct_signal, include/ss/ss.h:79-86)."""
+        if _is_cuda(X):
+            import torch
+            X = _as_torch(X)
+            X = X.reshape(1, -1) if X.ndim == 1 else X
+            want = torch.float32 if self.dtype == np.float32 else torch.float64
+            if X.dtype != want or X.shape[1] != self.shape[1] or X.device.index != self.device:
+                raise ValueError(f"coefficients must be a (batch, {self.shape[1]}) {want} tensor on cuda:{self.device}")
+            X = X if X.stride(1) == 1 else X.contiguous()
+            with torch.cuda.device(self.device):
+                Y = torch.empty((X.shape[0], self.shape[0]), dtype=X.dtype, device=X.device)
+                check(getattr(lib(), f"ssb200_reconstruct_batch_dev_{self._sfx}")(
+                    self._h, C.c_void_p(X.data_ptr()), C.c_size_t(X.shape[0]), C.c_size_t(X.stride(0)), C.c_void_p(Y.data_ptr()),
+                    C.c_size_t(Y.stride(0)), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            return Y
         X = np.ascontiguousarray(np.atleast_2d(X), dtype=self.dtype)
         Y = np.empty((X.shape[0], self.shape[0]), dtype=self.dtype)
         check(getattr(lib(), f"ssb200_reconstruct_batch_{self._sfx}")(
