@@ -6,6 +6,7 @@ import subprocess
 import sys
 
 rep = sys.argv[1]
+traffic_out = sys.argv[sys.argv.index("--traffic") + 1] if "--traffic" in sys.argv else None   # merge DRAM bytes per launch into this json
 WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
         "lts__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -24,6 +25,29 @@ for r in rows[2:]:
     for w in WANT:
         if w in idx:
             print(f"   {w:68s} {r[idx[w]]:>16s} {units[idx[w]]}")
+if traffic_out:
+    import json, os, re
+    UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+    def bench_name(n):   # the names bench.py's `kernels` entries carry
+        if "contract_x3_pair_kernel" in n:
+            return "contract_x3_pair_kernel"
+        if "homotopy_algebra_kernel" in n:
+            return "homotopy_algebra_kernel"
+        m = re.search(r"homotopy_scan_kernel<[^>]*,\s*(\(bool\))?(\w+)>", n)
+        if m:
+            return "homotopy_scan_kernel (q from Gram rows)" if m.group(2) in ("1", "true") else "homotopy_scan_kernel (Q streamed)"
+        return None
+    out = json.load(open(traffic_out)) if os.path.exists(traffic_out) else {"bytes_per_launch": {}, "source": {}}
+    for r in rows[2:]:
+        bn = bench_name(r[idx["Kernel Name"]])
+        if bn is None:
+            continue
+        tot = sum(float(r[idx[k]].replace(",", "")) * UNIT[units[idx[k]]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        grid = r[idx["launch__grid_size"]]
+        out["bytes_per_launch"][bn] = tot
+        out["source"][bn] = f"{os.path.basename(rep)}: {r[idx['Kernel Name']][:70]}, grid {grid}, {r[idx['gpu__time_duration.sum']]} {units[idx['gpu__time_duration.sum']]}"
+    json.dump(out, open(traffic_out, "w"), indent=1)
 for pat in sorted(set(n.split("(")[0].split("<")[0].split("::")[-1].split()[-1] for n in names)):
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + pat],
                          capture_output=True, text=True).stdout
