@@ -115,7 +115,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("BENCH_CLOCK_MS", "20")],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -441,7 +441,7 @@ def run_b200(args, cfg):
     ms_prof = p0.elapsed_time(p1)
     clocks = sampler.stop() if rank == 0 else None
     solver.set_timing(False)
-    counters, timing = solver.counters(), solver.timing()
+    counters, timing, prof = solver.counters(), solver.timing(), solver.kernel_profile()
     iters_mean = float(dIt.to(torch.float64).mean().item())
     converged = float((dErr <= cfg["tol"]).to(torch.float64).mean().item())
 
@@ -498,7 +498,6 @@ def run_b200(args, cfg):
                 "path": ("tcgen05 3-split, tf32 containers" if tf32 else "tcgen05 3-split, fp16 containers") if tensor_path else "simt fp32"}
     # every kernel class of the lockstep loop against its own bound (the scan kernels are HBM-streaming: c read + written,
     # q read when it comes from the contraction; algorithmic bytes per signal-iteration = 3 (or 2) x Npad x sizeof(T))
-    prof = solver.kernel_profile()
     npad = -(-N // 128) * 128
     isz_k = dt.itemsize
     hbm_peak = peaks["hbm_gbs"]

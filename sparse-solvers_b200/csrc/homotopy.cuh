@@ -7,6 +7,8 @@
 #include <algorithm>
 #include <atomic>
 #include <exception>
+#include <future>
+#include <cstring>
 #include <memory>
 #include <mutex>
 #include <thread>
@@ -163,6 +165,11 @@ private:
         dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, mask, act[2], counts;
         // host-pointer entry: double-buffered staging and the stream its copy-outs run on
         dev_buffer stY[2], stX[2], stIt[2], stErr[2];
+        // ... sparse return: the coefficients travel as (index, value) x Kmax + count per signal and are scattered into the
+        // caller's zero-filled X by a host task (40 MB instead of 537 MB over PCIe at C2)
+        dev_buffer stIdx[2], stVal[2], stCnt[2];
+        pinned_buffer hIdx[2], hVal[2], hCnt[2];
+        std::future<void> fin[2];
         cudaStream_t copy_out = nullptr;
         cudaEvent_t ev_out[2] = { nullptr, nullptr };
         int toggle = 0;

@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cstdlib>
+#include <functional>
 
 namespace ssb {
 
@@ -548,7 +549,11 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     // two, small, copy-outs.  C2 (tools/e2e_probe.py): one piece 47.9 ms/step, of which 2.5 copy-in and 7 copy-out.
     std::vector<size_t> sizes;
     {
-        static const double taper[] = { 0.25, 0.25, 0.1875, 0.1875, 0.0625, 0.0625 };
+        std::vector<double> taper = { 0.25, 0.25, 0.1875, 0.1875, 0.0625, 0.0625 };
+        if (const char* e = getenv("SSB200_TAPER")) {                                                  // tuning knob: "f1,f2,..."
+            taper.clear();
+            for (const char* q = e; *q;) { char* end; const double f = strtod(q, &end); if (end == q) break; taper.push_back(f); q = *end ? end + 1 : end; }
+        }
         size_t left = batch;
         if (const char* e = getenv("SSB200_HOST_PIECES")) {                                            // tuning knob: equal pieces
             const size_t n = (size_t)std::max(1, atoi(e)), per = std::min(cap, round_up((batch + n - 1) / n, 256));
@@ -563,6 +568,35 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
             while (left) { sizes.push_back(std::min(cap, left)); left -= sizes.back(); }
         }
     }
+    // Sparse return: a solution has at most kmax non-zeros, so when the rows are much wider than that the coefficients cross
+    // PCIe compacted (compress_rows_kernel) and are scattered into X on the host, while X itself is zero-filled by helper
+    // threads under the first pieces' kernels.  The caller sees the same dense X.
+    bool sparse_out = batch >= 4096 && (size_t)N >= 8 * (size_t)kmax;
+    if (const char* e = getenv("SSB200_HOST_SPARSE")) sparse_out = sparse_out && atoi(e) != 0;             // tuning knob
+    std::vector<std::thread> zero_threads;
+    std::mutex zero_mu;
+    bool zero_joined = false;
+    auto ensure_zeroed = [&] {
+        std::lock_guard<std::mutex> g(zero_mu);
+        if (!zero_joined) { for (auto& t : zero_threads) t.join(); zero_joined = true; }
+    };
+    if (sparse_out) {
+        int nz = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency() / 2));
+        if (const char* e = getenv("SSB200_ZERO_THREADS")) nz = std::max(1, std::min(64, atoi(e)));      // tuning knob
+        const size_t per = (batch + nz - 1) / nz;
+        for (int t = 0; t < nz; ++t) {
+            const size_t r0 = std::min(batch, (size_t)t * per), r1 = std::min(batch, r0 + per);
+            if (r0 == r1) continue;
+            zero_threads.emplace_back([=] {
+                if (ldx == (size_t)N) std::memset(X + r0 * ldx, 0, (r1 - r0) * (size_t)N * sizeof(T));
+                else for (size_t r = r0; r < r1; ++r) std::memset(X + r * ldx, 0, (size_t)N * sizeof(T));
+            });
+        }
+    }
+    struct join_guard { std::function<void()> f; ~join_guard() { f(); } } zero_guard{ [&] {   // also on the error paths
+        for (auto& l : lanes_) for (auto& f : l->fin) if (f.valid()) f.wait();
+        ensure_zeroed();
+    } };
     const size_t big = *std::max_element(sizes.begin(), sizes.end());
     std::vector<size_t> start(sizes.size() + 1, 0);
     for (size_t c = 0; c < sizes.size(); ++c) start[c + 1] = start[c] + sizes[c];
@@ -579,6 +613,11 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
             L.stX[i].reserve(big * N * sizeof(T));
             L.stIt[i].reserve(big * sizeof(uint32_t));
             L.stErr[i].reserve(big * sizeof(double));
+            if (sparse_out) {
+                L.stIdx[i].reserve(big * kmax * sizeof(int)); L.hIdx[i].reserve(big * kmax * sizeof(int));
+                L.stVal[i].reserve(big * kmax * sizeof(T));   L.hVal[i].reserve(big * kmax * sizeof(T));
+                L.stCnt[i].reserve(big * sizeof(int));        L.hCnt[i].reserve(big * sizeof(int));
+            }
         }
         L.toggle = 0;
     }
@@ -586,12 +625,42 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     run_lanes(nlanes, sizes.size(), [&](Lane& L, size_t c) {
         const int b = L.toggle; L.toggle ^= 1;
         const size_t b0 = start[c], rows = sizes[c];
+        if (L.fin[b].valid()) L.fin[b].get();                      // ... and its host-side scatter is done with the pinned pair
         SSB_CUDA(cudaStreamWaitEvent(L.stream, L.ev_out[b], 0));   // the piece before last has left this staging pair
         SSB_CUDA(cudaMemcpy2DAsync(L.stY[b].p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
                                    cudaMemcpyHostToDevice, L.stream));
         solve_chunk(L, L.stY[b].template as<T>(), rows, M, tol, max_iter, L.stX[b].template as<T>(), N,
                     L.stIt[b].template as<uint32_t>(), L.stErr[b].template as<double>());   // returns with the stream drained
         if (nocopy) return;
+        if (sparse_out) {
+            int* d_idx = L.stIdx[b].template as<int>(); T* d_val = L.stVal[b].template as<T>(); int* d_cnt = L.stCnt[b].template as<int>();
+            int* h_idx = L.hIdx[b].template as<int>();  T* h_val = L.hVal[b].template as<T>();  int* h_cnt = L.hCnt[b].template as<int>();
+            compress_rows_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, L.copy_out>>>(L.stX[b].template as<T>(), (size_t)N, N, rows, kmax,
+                                                                                      d_idx, d_val, d_cnt);
+            SSB_CUDA(cudaGetLastError());
+            L.counters[0]++;
+            SSB_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, rows * sizeof(int), cudaMemcpyDeviceToHost, L.copy_out));
+            SSB_CUDA(cudaMemcpyAsync(h_idx, d_idx, rows * kmax * sizeof(int), cudaMemcpyDeviceToHost, L.copy_out));
+            SSB_CUDA(cudaMemcpyAsync(h_val, d_val, rows * kmax * sizeof(T), cudaMemcpyDeviceToHost, L.copy_out));
+            SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt[b].p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.copy_out));
+            SSB_CUDA(cudaMemcpyAsync(errs + b0, L.stErr[b].p, rows * sizeof(double), cudaMemcpyDeviceToHost, L.copy_out));
+            SSB_CUDA(cudaEventRecord(L.ev_out[b], L.copy_out));
+            cudaEvent_t ev = L.ev_out[b];
+            const int dev = device, cap_k = kmax;
+            L.fin[b] = std::async(std::launch::async, [=, &ensure_zeroed] {
+                cudaSetDevice(dev);
+                SSB_CUDA(cudaEventSynchronize(ev));
+                ensure_zeroed();
+                for (size_t r = 0; r < rows; ++r) {
+                    const int n = std::min(h_cnt[r], cap_k);
+                    T* xr = X + (b0 + r) * ldx;
+                    const int* ir = h_idx + r * cap_k;
+                    const T* vr = h_val + r * cap_k;
+                    for (int k = 0; k < n; ++k) xr[ir[k]] = vr[k];
+                }
+            });
+            return;
+        }
         SSB_CUDA(cudaMemcpy2DAsync(X + b0 * ldx, ldx * sizeof(T), L.stX[b].p, N * sizeof(T), N * sizeof(T), rows,
                                    cudaMemcpyDeviceToHost, L.copy_out));
         SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt[b].p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.copy_out));
@@ -599,6 +668,7 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         SSB_CUDA(cudaEventRecord(L.ev_out[b], L.copy_out));
     });
     for (int li = 0; li < nlanes; ++li) SSB_CUDA(cudaStreamSynchronize(lane(li).copy_out));
+    for (int li = 0; li < nlanes; ++li) for (auto& f : lane(li).fin) if (f.valid()) f.get();
 }
 
 template <typename T>

@@ -101,3 +101,24 @@ def test_float64_and_argument_checks(case):
         ss.Irls(torch.from_numpy(A.T.copy()).cuda())
     X0, it0, e0 = s.solve_batch(torch.zeros((0, 128), dtype=torch.float32, device="cuda"), 1e-3, 40)
     assert X0.shape == (0, 512) and it0.numel() == 0
+
+
+@pytest.mark.parametrize("pad", [0, 24])
+def test_host_entry_sparse_return_equals_device_entry(pad):
+    """Large host batches return their coefficients compacted over PCIe and scattered into the caller's zero-filled X
+    (solve_batch_host: sparse_out); the caller must see exactly the dense X of the device-pointer entry, in a padded X too,
+    and whatever the buffer held before."""
+    import torch
+    import sparsesolvers as ss
+    from sparsesolvers import synth
+    A = synth.dictionary(128, 1024, dtype=np.float32, seed=41)
+    Y, _ = synth.sparse_signals(A, 8192 + 77, 8, seed=42)
+    s = ss.Homotopy(A)
+    dX, dit, derr = s.solve_batch(torch.from_numpy(Y).cuda(), 1e-3, 40)
+    wide = np.full((Y.shape[0], 1024 + pad), np.float32(3.5))
+    X, it, err = s.solve_batch(Y, 1e-3, 40, out=wide[:, :1024])
+    assert X.base is wide or X is wide or np.shares_memory(X, wide)
+    assert np.array_equal(X, dX.cpu().numpy())
+    assert (it == dit.cpu().numpy().astype(np.uint32)).all() and np.array_equal(err, derr.cpu().numpy())
+    if pad:
+        assert (wide[:, 1024:] == np.float32(3.5)).all()       # columns outside the view are not touched

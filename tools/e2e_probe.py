@@ -13,16 +13,18 @@ hY = torch.from_numpy(Y).pin_memory(); hX = torch.empty((65536, 2048)).pin_memor
 hIt = torch.empty(65536, dtype=torch.int32).pin_memory(); hErr = torch.empty(65536, dtype=torch.float64).pin_memory()
 def run():
     s.solve_batch_ptr(hY.data_ptr(), 65536, 512, hX.data_ptr(), 2048, hIt.data_ptr(), hErr.data_ptr(), 1e-3, 80, False)
-for label, env in (("default", {}), ("nocopy", {"SSB200_HOST_NOCOPY": "1"}), ("1 piece", {"SSB200_HOST_PIECES": "1"}),
-                   ("2 pieces", {"SSB200_HOST_PIECES": "2"}), ("4 pieces", {"SSB200_HOST_PIECES": "4"}),
-                   ("8 pieces", {"SSB200_HOST_PIECES": "8"}), ("default again", {})):
-    for k in ("SSB200_HOST_NOCOPY", "SSB200_HOST_PIECES"):
+for label, env in (("default", {}), ("dense copy-out", {"SSB200_HOST_SPARSE": "0"}), ("nocopy", {"SSB200_HOST_NOCOPY": "1"}), ("1 piece", {"SSB200_HOST_PIECES": "1"}),
+                   ("2 pieces", {"SSB200_HOST_PIECES": "2"}), ("3 pieces", {"SSB200_HOST_PIECES": "3"}), ("4 pieces", {"SSB200_HOST_PIECES": "4"}),
+                   ("8 pieces", {"SSB200_HOST_PIECES": "8"}), ("4 zero threads", {"SSB200_ZERO_THREADS": "4"}), ("16 zero threads", {"SSB200_ZERO_THREADS": "16"}),
+                   ("default again", {})):
+    for k in ("SSB200_HOST_NOCOPY", "SSB200_HOST_PIECES", "SSB200_HOST_SPARSE", "SSB200_ZERO_THREADS"):
         os.environ.pop(k, None)
     os.environ.update(env)
     run(); run()
-    t0 = time.perf_counter()
-    for _ in range(3): run()
-    print(label, "ms/step %.2f" % ((time.perf_counter() - t0) / 3 * 1e3), flush=True)
+    ts = []
+    for _ in range(8):
+        t0 = time.perf_counter(); run(); ts.append((time.perf_counter() - t0) * 1e3)
+    print(label, "ms/step median %.2f min %.2f max %.2f" % (np.median(ts), min(ts), max(ts)), flush=True)
 d = torch.empty((65536, 2048), device="cuda")
 torch.cuda.synchronize(); t0 = time.perf_counter(); hX.copy_(d, non_blocking=True); torch.cuda.synchronize()
 print("D2H 537 MB ms %.2f" % ((time.perf_counter() - t0) * 1e3))
