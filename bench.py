@@ -158,14 +158,15 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-def ncu_traffic():
-    """DRAM bytes per full-batch launch (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel, from the committed
-    `ncu --set full` capture of this same command (profiles/ncu_traffic.json, written by tools/ncu_summary.py --traffic)."""
+def ncu_traffic(config):
+    """DRAM bytes per full-chunk launch (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/ncu_traffic.json, written by tools/ncu_summary.py --traffic);
+    captures exist for the configurations listed there only."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if not os.path.exists(p):
         return {}
     with open(p) as f:
-        return json.load(f).get("bytes_per_launch", {})
+        return json.load(f).get(config, {}).get("bytes_per_launch", {})
 
 
 def run_reference(args, cfg):
@@ -458,11 +459,13 @@ def run_b200(args, cfg):
                                    cfg["tol"], cfg["max_iter"], False)
         step_host()
         barrier()
+        solver.reset_counters()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             step_host()
         barrier()
         e2e_s = time.perf_counter() - t0
+        h2d_b, d2h_b = solver.transfer_bytes()        # counted by the library from the copies it issues
         assert torch.equal(hIt, dIt.cpu()), "host-pointer and device-pointer entries disagree"
     if world > 1:
         t = torch.tensor([ms, e2e_s if not args.no_e2e else 0.0], dtype=torch.float64, device=dev)
@@ -473,7 +476,10 @@ def run_b200(args, cfg):
     if not args.no_e2e:
         isz = dt.itemsize
         e2e = {"value": world * batch * args.steps / e2e_max, "unit": "signals/s",
-               "h2d_bytes_per_step": world * batch * M * isz, "d2h_bytes_per_step": world * batch * (N * isz + 4 + 8)}
+               "h2d_bytes_per_step": world * h2d_b // args.steps, "d2h_bytes_per_step": world * d2h_b // args.steps,
+               "result": "dense X (batch x N) in the caller's pinned host buffer; over PCIe the coefficients travel as "
+                         "(index, value) x Kmax + count per signal when N >= 8 Kmax, dense otherwise",
+               "dense_result_bytes_per_step": world * batch * (N * isz + 4 + 8)}
 
     if rank != 0:
         if world > 1:
@@ -496,38 +502,41 @@ def run_b200(args, cfg):
                 "launches": counters["contractions"], "avg_launch_ms": timing["contraction_ms"] / max(1, counters["contractions"]),
                 "share_of_step": timing["contraction_ms"] / ms_prof, "step_kernel_share": timing["step_ms"] / ms_prof,
                 "path": ("tcgen05 3-split, tf32 containers" if tf32 else "tcgen05 3-split, fp16 containers") if tensor_path else "simt fp32"}
-    # every kernel class of the lockstep loop against its own bound (the scan kernels are HBM-streaming: c read + written,
-    # q read when it comes from the contraction; algorithmic bytes per signal-iteration = 3 (or 2) x Npad x sizeof(T))
-    npad = -(-N // 128) * 128
-    isz_k = dt.itemsize
+    # every kernel class of the lockstep loop against its own bound.  Algorithmic HBM bytes are counted by the library
+    # (ssb200_get_kernel_bytes): c read + written, q read when it was streamed, the K x K inverse read + written, the next
+    # right-hand side written.  `traffic` = DRAM bytes of one full-chunk launch from the committed ncu --set full capture.
     hbm_peak = peaks["hbm_gbs"]
-    traffic = ncu_traffic()
+    traffic = ncu_traffic(args.config)
 
-    def hbm_entry(name, ms_k, rows_k, bytes_k, launches_note):
+    def hbm_entry(name, classes, note, bound="hbm"):
+        ms_k = sum(prof[c]["ms"] for c in classes)
         if ms_k <= 0:
             return None
+        rows_k = sum(prof[c]["rows"] for c in classes)
+        bytes_k = sum(prof[c]["algorithmic_bytes"] for c in classes)
         gbs = bytes_k / (ms_k * 1e-3) / 1e9
-        return {"kernel": name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
-                "traffic": traffic.get(name), "peak_source": f"{peak_src} hbm_gbs", "signal_rows": rows_k,
-                "share_of_step": ms_k / ms_prof, "algorithmic_bytes": launches_note}
-    k_stream = hbm_entry("homotopy_scan_kernel (Q streamed)", prof["scan_stream"]["ms"], prof["scan_stream"]["rows"],
-                         3.0 * npad * isz_k * prof["scan_stream"]["rows"], "3 x Npad x sizeof(T) per signal-iteration: c read, q read, c written")
-    k_gram = hbm_entry("homotopy_scan_kernel (q from Gram rows)", prof["scan_gram"]["ms"], prof["scan_gram"]["rows"],
-                       2.0 * npad * isz_k * prof["scan_gram"]["rows"], "2 x Npad x sizeof(T) per signal-iteration: c read, c written; "
-                       "K rows of G per signal come from L2 (L2-bound, see DESIGN.md)")
-    scan_ms = prof["scan_stream"]["ms"] + prof["scan_gram"]["ms"]
-    k_scan = hbm_entry("homotopy_scan_kernel (both variants)", scan_ms, prof["scan_stream"]["rows"] + prof["scan_gram"]["rows"],
-                       npad * isz_k * (3.0 * prof["scan_stream"]["rows"] + 2.0 * prof["scan_gram"]["rows"]),
-                       "sum of the two variants")
-    k_alg = {"kernel": "homotopy_algebra_kernel", "bound": "l2 / latency (K x K inverse update per warp, K-atom gather from L2)",
-             "signal_rows": prof["algebra"]["rows"], "share_of_step": prof["algebra"]["ms"] / ms_prof,
-             "us_per_1k_rows": 1e6 * prof["algebra"]["ms"] / max(1, prof["algebra"]["rows"]),
-             "traffic": traffic.get("homotopy_algebra_kernel")} if prof["algebra"]["ms"] > 0 else None
+        tr = [traffic[KERNEL_NAMES[c]] * prof[c]["rows"] for c in classes if KERNEL_NAMES[c] in traffic and prof[c]["rows"]]
+        return {"kernel": name, "bound": bound, "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+                "traffic": sum(tr) / rows_k if len(tr) == len([c for c in classes if prof[c]["rows"]]) and rows_k else None,
+                "traffic_note": "DRAM bytes per full-chunk launch (ncu), row-weighted over the variants",
+                "peak_source": f"{peak_src} hbm_gbs", "signal_rows": rows_k, "algorithmic_bytes_per_row": bytes_k / max(1, rows_k),
+                "share_of_step": ms_k / ms_prof, "algorithmic_bytes": note}
+    KERNEL_NAMES = {"scan_stream": "homotopy_scan_kernel (Q streamed)", "scan_gram": "homotopy_scan_kernel (q from Gram rows)",
+                    "algebra": "homotopy_algebra_kernel", "step_mono": "homotopy_step_kernel"}
+    k_stream = hbm_entry(KERNEL_NAMES["scan_stream"], ["scan_stream"], "3 x Npad x sizeof(T) per signal-iteration: c read, q read, c written")
+    k_gram = hbm_entry(KERNEL_NAMES["scan_gram"], ["scan_gram"], "2 x Npad x sizeof(T) per signal-iteration: c read, c written; the K rows of G "
+                       "per signal come from L2, which is what bounds this variant (DESIGN.md 3)")
+    k_scan = hbm_entry("homotopy_scan_kernel (both variants)", ["scan_stream", "scan_gram"], "sum of the two variants")
+    k_alg = hbm_entry(KERNEL_NAMES["algebra"], ["algebra"], "K x K inverse read + written (K <= iteration number), next right-hand side written; "
+                      "the K-atom gather of p = A_G d comes from L2, which is what bounds it", bound="hbm (L2-bound in practice)")
+    k_mono = hbm_entry("homotopy_step_kernel (scan + algebra in one CTA per signal: large active sets, small batches)", ["step_mono"],
+                       "3 x Npad x sizeof(T) + K x K inverse read + written + right-hand side written, per signal-iteration")
     roofline["traffic"] = traffic.get("contract_x3_pair_kernel")
-    kernels = [k for k in (roofline, k_scan, k_stream, k_gram, k_alg) if k]
+    kernels = [k for k in (roofline, k_scan, k_stream, k_gram, k_alg, k_mono) if k]
     # `roofline` names the kernel with the largest measured share of the step
-    if k_scan and k_scan["share_of_step"] > roofline["share_of_step"]:
-        roofline = dict(k_scan)
+    for k in (k_scan, k_mono):
+        if k and k["share_of_step"] > roofline["share_of_step"]:
+            roofline = dict(k)
     whole = {"achieved": 2.0 * M * N * world * batch * args.steps * (iters_mean + 1) / (ms * 1e-3) / 1e12,
              "unit": "TFLOP/s", "note": "whole-solve algorithmic flops 2*M*N*(iters+1) per signal / step time"}
     whole["frac"] = whole["achieved"] / (peak * world)

@@ -171,6 +171,11 @@ int ssb200_get_timing(void* handle, double ms[2]);
  *   class 0 contraction, 1 all step kernels, 2 scan kernel with Q streamed from HBM, 3 scan kernel with q formed from the
  *   Gram matrix, 4 algebra kernel, 5 monolithic step / init kernels */
 int ssb200_get_kernel_profile(void* handle, double ms[6], uint64_t rows[6]);
+/* algorithmic HBM bytes of the launches of classes 2-5 above (c read + written, q read when streamed, the K x K inverse read +
+ * written with K bounded by the iteration number, the next right-hand side written), summed like the profile's rows */
+int ssb200_get_kernel_bytes(void* handle, uint64_t bytes[6]);
+/* bytes[0] = host->device, bytes[1] = device->host bytes the host-pointer batch entries copied since the last reset */
+int ssb200_get_transfer_bytes(void* handle, uint64_t bytes[2]);
 int ssb200_set_contraction_path(void* handle, int path);
 /* test / bench hook for the contraction kernel alone: Q[r][n] = sum_m A[m][n] * P[r][m] for `rows` host rows
  * (P: rows x M, Q: rows x N, both dense row-major), computed by path 1 (SIMT) or 2 (tcgen05, float32);

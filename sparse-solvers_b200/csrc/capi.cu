@@ -267,7 +267,7 @@ void ssb200_destroy(void* handle)
 
 int ssb200_reset_counters(void* h)
 { return guarded([&] { SSB_REQUIRE(h, "null handle"); auto* b = static_cast<SolverBase*>(h);
-                       for (auto& c : b->counters) c = 0; for (auto& m : b->ms) m = 0.0; for (auto& r : b->kernel_rows) r = 0; }); }
+                       for (auto& c : b->counters) c = 0; for (auto& m : b->ms) m = 0.0; for (auto& r : b->kernel_rows) r = 0; for (auto& r : b->kernel_bytes) r = 0; b->h2d_bytes = 0; b->d2h_bytes = 0; }); }
 int ssb200_get_counters(void* h, uint64_t counters[4])
 { return guarded([&] { SSB_REQUIRE(h && counters, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        for (int i = 0; i < 4; ++i) counters[i] = b->counters[i]; }); }
@@ -278,6 +278,12 @@ int ssb200_get_timing(void* h, double ms[2])
 int ssb200_get_kernel_profile(void* h, double ms[6], uint64_t rows[6])
 { return guarded([&] { SSB_REQUIRE(h && ms && rows, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        for (int i = 0; i < SolverBase::NCLS; ++i) { ms[i] = b->ms[i]; rows[i] = b->kernel_rows[i]; } }); }
+int ssb200_get_kernel_bytes(void* h, uint64_t bytes[6])
+{ return guarded([&] { SSB_REQUIRE(h && bytes, "null pointer"); auto* b = static_cast<SolverBase*>(h);
+                       for (int i = 0; i < SolverBase::NCLS; ++i) bytes[i] = b->kernel_bytes[i]; }); }
+int ssb200_get_transfer_bytes(void* h, uint64_t bytes[2])
+{ return guarded([&] { SSB_REQUIRE(h && bytes, "null pointer"); auto* b = static_cast<SolverBase*>(h);
+                       bytes[0] = b->h2d_bytes.load(); bytes[1] = b->d2h_bytes.load(); }); }
 int ssb200_set_contraction_path(void* h, int path)
 { return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 3, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
 

@@ -393,9 +393,17 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
     for (uint32_t it = 1; it <= last; ++it) {
         const uint64_t n = (uint64_t)h_counts[it - 1];           // signals that entered iteration `it`
+        const uint64_t nc = (uint64_t)h_counts[it];              // ... and continue after it
+        const uint64_t kb = std::min<uint64_t>(it, (uint64_t)L.ws_kmax);
+        // algorithmic HBM bytes of the launch: c read + written, q read when it was streamed; the K x K inverse
+        // read + written (K <= kb = it); the next right-hand side written in its container format
+        const uint64_t cq = (uint64_t)Npad * sizeof(T), inv = 2 * kb * kb * sizeof(T), rhs = (uint64_t)Mp * (tc ? 4 : sizeof(T));
         L.rows[route[it]] += n;
-        if (route[it] != 5) L.rows[4] += (uint64_t)h_counts[it]; // the algebra kernel runs for those that continue
         L.rows[1] += n;
+        if (route[it] == 2) L.bytes[2] += n * 3 * cq;
+        if (route[it] == 3) L.bytes[3] += n * 2 * cq;
+        if (route[it] != 5) { L.rows[4] += nc; L.bytes[4] += nc * (inv + ((it + 1 < gram_iters) ? 0 : rhs)); }
+        else L.bytes[5] += n * 3 * cq + nc * (inv + rhs);
     }
 }
 
@@ -405,7 +413,7 @@ void Homotopy<T>::merge(Lane& L)
 {
     std::lock_guard<std::mutex> g(merge_mu_);
     for (int i = 0; i < 4; ++i) { counters[i] += L.counters[i]; L.counters[i] = 0; }
-    for (int i = 0; i < NCLS; ++i) { kernel_rows[i] += L.rows[i]; L.rows[i] = 0; }
+    for (int i = 0; i < NCLS; ++i) { kernel_rows[i] += L.rows[i]; L.rows[i] = 0; kernel_bytes[i] += L.bytes[i]; L.bytes[i] = 0; }
     for (auto& s : L.spans) {
         float t = 0.f;
         if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) ms[s.cls] += t;
@@ -629,6 +637,9 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         SSB_CUDA(cudaStreamWaitEvent(L.stream, L.ev_out[b], 0));   // the piece before last has left this staging pair
         SSB_CUDA(cudaMemcpy2DAsync(L.stY[b].p, M * sizeof(T), Y + b0 * ldy, ldy * sizeof(T), M * sizeof(T), rows,
                                    cudaMemcpyHostToDevice, L.stream));
+        h2d_bytes += rows * (size_t)M * sizeof(T);
+        d2h_bytes += rows * (sizeof(uint32_t) + sizeof(double)) +
+                     (sparse_out ? rows * ((size_t)kmax * (sizeof(int) + sizeof(T)) + sizeof(int)) : rows * (size_t)N * sizeof(T));
         solve_chunk(L, L.stY[b].template as<T>(), rows, M, tol, max_iter, L.stX[b].template as<T>(), N,
                     L.stIt[b].template as<uint32_t>(), L.stErr[b].template as<double>());   // returns with the stream drained
         if (nocopy) return;

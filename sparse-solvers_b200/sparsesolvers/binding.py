@@ -153,9 +153,16 @@ class _Solver:
 
     def kernel_profile(self):
         """Per kernel class of the lockstep loop: summed device ms (timing enabled) and signal-rows processed."""
-        ms, rows = (C.c_double * 6)(), (C.c_uint64 * 6)()
+        ms, rows, nbytes = (C.c_double * 6)(), (C.c_uint64 * 6)(), (C.c_uint64 * 6)()
         check(lib().ssb200_get_kernel_profile(self._h, ms, rows))
-        return {k: dict(ms=ms[i], rows=int(rows[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+        check(lib().ssb200_get_kernel_bytes(self._h, nbytes))
+        return {k: dict(ms=ms[i], rows=int(rows[i]), algorithmic_bytes=int(nbytes[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes the host-pointer batch entry copied since the last reset_counters()."""
+        b = (C.c_uint64 * 2)()
+        check(lib().ssb200_get_transfer_bytes(self._h, b))
+        return int(b[0]), int(b[1])
 
     def set_contraction_path(self, path):
         check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path])))

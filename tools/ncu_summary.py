@@ -38,7 +38,9 @@ if traffic_out:
         if m:
             return "homotopy_scan_kernel (q from Gram rows)" if m.group(2) in ("1", "true") else "homotopy_scan_kernel (Q streamed)"
         return None
-    out = json.load(open(traffic_out)) if os.path.exists(traffic_out) else {"bytes_per_launch": {}, "source": {}}
+    cfg_name = sys.argv[sys.argv.index("--config") + 1] if "--config" in sys.argv else "C2"
+    whole = json.load(open(traffic_out)) if os.path.exists(traffic_out) else {}
+    out = whole.setdefault(cfg_name, {"bytes_per_launch": {}, "source": {}})
     for r in rows[2:]:
         bn = bench_name(r[idx["Kernel Name"]])
         if bn is None:
@@ -47,7 +49,7 @@ if traffic_out:
         grid = r[idx["launch__grid_size"]]
         out["bytes_per_launch"][bn] = tot
         out["source"][bn] = f"{os.path.basename(rep)}: {r[idx['Kernel Name']][:70]}, grid {grid}, {r[idx['gpu__time_duration.sum']]} {units[idx['gpu__time_duration.sum']]}"
-    json.dump(out, open(traffic_out, "w"), indent=1)
+    json.dump(whole, open(traffic_out, "w"), indent=1)
 for pat in sorted(set(n.split("(")[0].split("<")[0].split("::")[-1].split()[-1] for n in names)):
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + pat],
                          capture_output=True, text=True).stdout
