@@ -589,7 +589,10 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         if (!zero_joined) { for (auto& t : zero_threads) t.join(); zero_joined = true; }
     };
     if (sparse_out) {
-        int nz = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency() / 2));
+        // helper threads: half the host cores, shared between the GPUs of the box (one process per GPU each runs this), 2..8
+        int ngpu = 1;
+        if (cudaGetDeviceCount(&ngpu) != cudaSuccess || ngpu < 1) { ngpu = 1; cudaGetLastError(); }
+        int nz = (int)std::max(2u, std::min(8u, std::thread::hardware_concurrency() / (2u * (unsigned)ngpu)));
         if (const char* e = getenv("SSB200_ZERO_THREADS")) nz = std::max(1, std::min(64, atoi(e)));      // tuning knob
         const size_t per = (batch + nz - 1) / nz;
         for (int t = 0; t < nz; ++t) {
