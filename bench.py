@@ -458,7 +458,8 @@ def run_b200(args, cfg):
         def step_host():
             solver.solve_batch_ptr(hY.data_ptr(), batch, M, hX.data_ptr(), N, hIt.data_ptr(), hErr.data_ptr(),
                                    cfg["tol"], cfg["max_iter"], False)
-        step_host()
+        for _ in range(max(3, args.warmup)):          # warm-up of the host-pointer entry (staging buffers, lanes, helper threads)
+            step_host()
         barrier()
         solver.reset_counters()
         t0 = time.perf_counter()
@@ -527,6 +528,12 @@ def run_b200(args, cfg):
     k_stream = hbm_entry(KERNEL_NAMES["scan_stream"], ["scan_stream"], "3 x Npad x sizeof(T) per signal-iteration: c read, q read, c written")
     k_gram = hbm_entry(KERNEL_NAMES["scan_gram"], ["scan_gram"], "2 x Npad x sizeof(T) per signal-iteration: c read, c written; the K rows of G "
                        "per signal come from L2, which is what bounds this variant (DESIGN.md 3)")
+    if k_gram:   # what actually bounds this variant: K rows of G per signal through L2, on top of the HBM stream
+        l2_gbs = (prof["scan_gram"]["l2_bytes"] + prof["scan_gram"]["algorithmic_bytes"]) / (prof["scan_gram"]["ms"] * 1e-3) / 1e9
+        k_gram["l2"] = {"achieved": l2_gbs, "peak": 12000.0, "unit": "GB/s", "frac": l2_gbs / 12000.0,
+                        "peak_source": "this repo's own measurement of L2 -> SM streaming on B200 (TMA operand stream of the contraction with "
+                                       "everything else switched off, tools/tc_dbg.py, DESIGN.md 3); not in MEASURED_PEAKS.json",
+                        "bytes": "K <= iteration-number rows of G (Npad x sizeof(T) each) per signal + the c stream"}
     k_scan = hbm_entry("homotopy_scan_kernel (both variants)", ["scan_stream", "scan_gram"], "sum of the two variants")
     k_alg = hbm_entry(KERNEL_NAMES["algebra"], ["algebra"], "K x K inverse read + written (K <= iteration number), next right-hand side written; "
                       "the K-atom gather of p = A_G d comes from L2, which is what bounds it", bound="hbm (L2-bound in practice)")

@@ -173,7 +173,7 @@ int ssb200_get_timing(void* handle, double ms[2]);
 int ssb200_get_kernel_profile(void* handle, double ms[6], uint64_t rows[6]);
 /* algorithmic HBM bytes of the launches of classes 2-5 above (c read + written, q read when streamed, the K x K inverse read +
  * written with K bounded by the iteration number, the next right-hand side written), summed like the profile's rows */
-int ssb200_get_kernel_bytes(void* handle, uint64_t bytes[6]);
+int ssb200_get_kernel_bytes(void* handle, uint64_t bytes[8]);   /* [6] = L2 bytes of the Gram rows read by class 3, [7] unused */
 /* bytes[0] = host->device, bytes[1] = device->host bytes the host-pointer batch entries copied since the last reset */
 int ssb200_get_transfer_bytes(void* handle, uint64_t bytes[2]);
 int ssb200_set_contraction_path(void* handle, int path);

@@ -278,9 +278,9 @@ int ssb200_get_timing(void* h, double ms[2])
 int ssb200_get_kernel_profile(void* h, double ms[6], uint64_t rows[6])
 { return guarded([&] { SSB_REQUIRE(h && ms && rows, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        for (int i = 0; i < SolverBase::NCLS; ++i) { ms[i] = b->ms[i]; rows[i] = b->kernel_rows[i]; } }); }
-int ssb200_get_kernel_bytes(void* h, uint64_t bytes[6])
+int ssb200_get_kernel_bytes(void* h, uint64_t bytes[8])
 { return guarded([&] { SSB_REQUIRE(h && bytes, "null pointer"); auto* b = static_cast<SolverBase*>(h);
-                       for (int i = 0; i < SolverBase::NCLS; ++i) bytes[i] = b->kernel_bytes[i]; }); }
+                       for (int i = 0; i < 8; ++i) bytes[i] = b->kernel_bytes[i]; }); }
 int ssb200_get_transfer_bytes(void* h, uint64_t bytes[2])
 { return guarded([&] { SSB_REQUIRE(h && bytes, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        bytes[0] = b->h2d_bytes.load(); bytes[1] = b->d2h_bytes.load(); }); }

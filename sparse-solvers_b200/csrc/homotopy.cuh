@@ -181,7 +181,7 @@ private:
         // instrumentation, merged into the handle after the solve
         uint64_t counters[4] = { 0, 0, 0, 0 };
         uint64_t rows[6] = { 0, 0, 0, 0, 0, 0 };   // signal-rows per launch class (SolverBase::kernel_rows)
-        uint64_t bytes[6] = { 0, 0, 0, 0, 0, 0 };  // algorithmic HBM bytes per launch class (SolverBase::kernel_bytes)
+        uint64_t bytes[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };  // algorithmic bytes per launch class (SolverBase::kernel_bytes)
         struct span { cudaEvent_t a, b; int cls; };
         std::vector<span> spans;
         std::vector<cudaEvent_t> pool;

@@ -401,7 +401,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         L.rows[route[it]] += n;
         L.rows[1] += n;
         if (route[it] == 2) L.bytes[2] += n * 3 * cq;
-        if (route[it] == 3) L.bytes[3] += n * 2 * cq;
+        if (route[it] == 3) { L.bytes[3] += n * 2 * cq; L.bytes[6] += n * kb * cq; }   // [6]: the K <= kb rows of G per signal, from L2
         if (route[it] != 5) { L.rows[4] += nc; L.bytes[4] += nc * (inv + ((it + 1 < gram_iters) ? 0 : rhs)); }
         else L.bytes[5] += n * 3 * cq + nc * (inv + rhs);
     }
@@ -413,7 +413,8 @@ void Homotopy<T>::merge(Lane& L)
 {
     std::lock_guard<std::mutex> g(merge_mu_);
     for (int i = 0; i < 4; ++i) { counters[i] += L.counters[i]; L.counters[i] = 0; }
-    for (int i = 0; i < NCLS; ++i) { kernel_rows[i] += L.rows[i]; L.rows[i] = 0; kernel_bytes[i] += L.bytes[i]; L.bytes[i] = 0; }
+    for (int i = 0; i < NCLS; ++i) { kernel_rows[i] += L.rows[i]; L.rows[i] = 0; }
+    for (int i = 0; i < 8; ++i) { kernel_bytes[i] += L.bytes[i]; L.bytes[i] = 0; }
     for (auto& s : L.spans) {
         float t = 0.f;
         if (cudaEventElapsedTime(&t, s.a, s.b) == cudaSuccess) ms[s.cls] += t;

@@ -153,10 +153,12 @@ class _Solver:
 
     def kernel_profile(self):
         """Per kernel class of the lockstep loop: summed device ms (timing enabled) and signal-rows processed."""
-        ms, rows, nbytes = (C.c_double * 6)(), (C.c_uint64 * 6)(), (C.c_uint64 * 6)()
+        ms, rows, nbytes = (C.c_double * 6)(), (C.c_uint64 * 6)(), (C.c_uint64 * 8)()
         check(lib().ssb200_get_kernel_profile(self._h, ms, rows))
         check(lib().ssb200_get_kernel_bytes(self._h, nbytes))
-        return {k: dict(ms=ms[i], rows=int(rows[i]), algorithmic_bytes=int(nbytes[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+        prof = {k: dict(ms=ms[i], rows=int(rows[i]), algorithmic_bytes=int(nbytes[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+        prof["scan_gram"]["l2_bytes"] = int(nbytes[6])       # the K rows of G per signal
+        return prof
 
     def transfer_bytes(self):
         """(host->device, device->host) bytes the host-pointer batch entry copied since the last reset_counters()."""
