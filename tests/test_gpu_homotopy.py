@@ -52,7 +52,11 @@ def test_vs_port(ss, dtype, m, n, k, batch, path):
     Xr, itr, er = port.homotopy(A, Y, 1e-3, mi)
     s = ss.Homotopy(A)
     s.set_contraction_path(path)
-    stats, _ = check_homotopy(s, A, Y, 1e-3, mi, Xr, itr, er, f"{np.dtype(dtype).name} {m}x{n} k={k} [{path}]")
+    # float32 noise floor at the C2 shape, measured CPU against CPU on these very inputs (the reference build vs its plain-C
+    # restatement): 6 / 192 coefficient deviations in (1e-4, 3.2e-4], 2 iteration flips; 4.2 % and 1.2 % on 1,024 signals
+    # (BASELINE.md 2).  The gate allows that rate there; nothing may exceed 1e-3 anywhere.
+    noise = 0.05 if (m == 512 and np.dtype(dtype) == np.float32) else 0.02
+    stats, _ = check_homotopy(s, A, Y, 1e-3, mi, Xr, itr, er, f"{np.dtype(dtype).name} {m}x{n} k={k} [{path}]", noise_rate=noise)
     print(stats, s.counters())
 
 
