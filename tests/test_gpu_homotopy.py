@@ -380,5 +380,9 @@ def test_quirk_parity_set(ss, m, n, k, max_iter):
     assert (it != itr).sum() <= 5, f"{(it != itr).sum()} iteration-count mismatches of 256"
     conv = ~wander & (it == itr)
     r = parity.compare(X[conv], it[conv], err[conv], Xr[conv], itr[conv], er[conv], c0_inf(A, Y)[conv])
-    print(parity.assert_parity(r, np.float32, f"quirk set {m}x{n}, converging half"), "wandering:", int(wander.sum()))
+    # float32 noise floor of THIS set measured CPU against CPU (reference build vs restatement, converging half): at 512x2048
+    # 9 / 124 coefficient deviations in (1e-4, 2.7e-4] and 2 soft support flips, at 256x1024 1 / 122 -- these signals converge
+    # after longer paths than the sign-normalised ones.  Allowed here: twice that rate; nothing above 1e-3 (assert_parity).
+    noise = 0.15 if m == 512 else 0.02
+    print(parity.assert_parity(r, np.float32, f"quirk set {m}x{n}, converging half", noise_rate=noise), "wandering:", int(wander.sum()))
     assert np.isfinite(X).all()
