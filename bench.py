@@ -41,6 +41,17 @@ CONFIGS = {
 }
 
 
+# stdout carries the ONE JSON line and nothing else: whatever libraries print there (NCCL's version banner is a plain printf)
+# is sent to stderr by pointing fd 1 at fd 2 for the whole run; the line itself goes to the saved descriptor.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -196,7 +207,7 @@ def run_reference(args, cfg):
         "e2e": {"value": value, "unit": "signals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_irls(args, cfg):
@@ -229,7 +240,7 @@ def run_irls(args, cfg):
                          "unit": "TFLOP/s", "frac": flops / secs / 1e12 / 40.0, "traffic": None,
                          "peak_source": "B200 FP64 datasheet (no measured FP64 figure in MEASURED_PEAKS.json); separately rounded mul/add cannot use FMA: half of it is the ceiling"},
             "cpu_baseline": None}
-    print(json.dumps(line))
+    emit(line)
 
 
 def grid_workload(M, N, seed=0):
@@ -301,7 +312,7 @@ def run_grid(args, cfg):
                                    "dictionary edited in place and refreshed before every solve"},
             "cells": cells, "cpu_baseline": {"kind": "reference", "cores": 1, "unit": "ms per solve, per cell (cells[].cpu_ms_per_solve)",
                                              "sample": f"{solves} solves per cell"} if have_ref else None}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_single(args, cfg):
@@ -346,7 +357,7 @@ def run_single(args, cfg):
                          "frac": nbytes / secs / 1e9 / peaks["hbm_gbs"], "traffic": None,
                          "note": "A (1 MB) is L2-resident: the bound that bites is three grid barriers + call overhead per iteration, not bandwidth"},
             "cpu_baseline": cpu}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_b200(args, cfg):
@@ -577,7 +588,7 @@ def run_b200(args, cfg):
                                   "timed region; shares are fractions of that pass"},
         "cpu_baseline": cpu, "clocks": clocks,
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

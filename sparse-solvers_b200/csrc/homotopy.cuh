@@ -254,6 +254,17 @@ private:
     }
     void apply_l2_policy(cudaStream_t st);
 
+    struct plan_key {
+        size_t batch; int kmax; bool host_path; int env_lanes, env_chunk;
+        bool operator==(const plan_key& o) const {
+            return batch == o.batch && kmax == o.kmax && host_path == o.host_path && env_lanes == o.env_lanes && env_chunk == o.env_chunk;
+        }
+    };
+    plan_key plan_key_{};
+    size_t plan_chunk_ = 0;
+    int plan_lanes_ = 0;
+    bool plan_valid_ = false;
+
     size_t bytes_per_signal(int kmax) const {
         return (size_t)(2 * Npad + 4 * Mp + (size_t)kmax * kmax + 2 * kmax + 4) * sizeof(T) + 6 * sizeof(int);
     }

@@ -1,6 +1,7 @@
 // Member definitions of ssb::Homotopy<T> (included by homotopy.cuh).
 #pragma once
 
+#include <chrono>
 #include <cstdlib>
 #include <functional>
 
@@ -50,6 +51,11 @@ void Homotopy<T>::apply_l2_policy(cudaStream_t st)
 template <typename T>
 void Homotopy<T>::plan_batch(size_t batch, int kmax, bool host_path, size_t& chunk, int& nlanes)
 {
+    // the plan of the previous call with the same shape is reused: cudaMemGetInfo goes through the resource manager and was
+    // measured to take 10-80 ms every few calls on a busy box (tools/variance.py: the only slow part of a slow step)
+    const char* env_l = getenv("SSB200_LANES"); const char* env_c = getenv("SSB200_CHUNK");
+    const plan_key key{ batch, kmax, host_path, env_l ? atoi(env_l) : -1, env_c ? atoi(env_c) : -1 };
+    if (plan_valid_ && key == plan_key_) { chunk = plan_chunk_; nlanes = plan_lanes_; return; }
     size_t free_b = 0, total_b = 0;
     SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
     size_t held = 0;
@@ -72,6 +78,7 @@ void Homotopy<T>::plan_batch(size_t batch, int kmax, bool host_path, size_t& chu
     chunk = (per + pieces - 1) / pieces;
     if (chunk > 256) chunk = round_up(chunk, 256);
     chunk = std::min(std::min(chunk, cap), batch);
+    plan_key_ = key; plan_chunk_ = chunk; plan_lanes_ = nlanes; plan_valid_ = true;
 }
 
 template <typename T>
@@ -321,7 +328,16 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     uint32_t seen = 0;           // ... which is counts[seen]
     uint32_t last = 0;
     std::vector<uint8_t> route((size_t)max_iter + 2, 0);   // launch class of every iteration's scan (kernel profile)
+    // debugging aid (SSB200_TRACE_STALL=<ms>): host timeline of a chunk that took longer than <ms> -- when each iteration was
+    // queued, how long the host waited for a count, which count it had then
+    double trace_ms = 0.0;
+    if (const char* e = getenv("SSB200_TRACE_STALL")) trace_ms = atof(e);
+    struct trace_row { double t_begin, t_wait, t_queued; uint32_t seen; size_t known; };
+    std::vector<trace_row> trace;
+    const auto t_chunk0 = std::chrono::steady_clock::now();
+    auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_chunk0).count(); };
     for (uint32_t it = 1; it <= max_iter; ++it) {
+        const double t_begin = trace_ms > 0 ? now_ms() : 0.0;
         const uint32_t must = async ? (it > RUN_AHEAD ? it - RUN_AHEAD : 0) : it - 1;   // counts[must] has to be in
         for (uint32_t j = seen + 1; j < it; ++j) {
             cudaEvent_t ev = L.count_events[j % (RUN_AHEAD + 1)];
@@ -330,6 +346,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
             seen = j;
             known = (size_t)h_counts[j];
         }
+        const double t_wait = trace_ms > 0 ? now_ms() : 0.0;
         if (known == 0) break;
         last = it;
         // While the active set is small (K <= it < gram_iters) q = G[:, active] d costs K rows of G per signal in the
@@ -387,9 +404,17 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         SSB_CUDA(cudaMemcpyAsync(h_counts + it, d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, L.side));
         SSB_CUDA(cudaEventRecord(L.count_events[it % (RUN_AHEAD + 1)], L.side));
         cur ^= 1;
+        if (trace_ms > 0) trace.push_back({ t_begin, t_wait, now_ms(), seen, known });
     }
+    const double t_loop = trace_ms > 0 ? now_ms() : 0.0;
     SSB_CUDA(cudaStreamSynchronize(st));
     SSB_CUDA(cudaStreamSynchronize(L.side));
+    if (trace_ms > 0 && now_ms() > trace_ms) {
+        fprintf(stderr, "[ssb200] slow chunk: %.2f ms (loop queued by %.2f ms, %zu rows)\n", now_ms(), t_loop, rows);
+        for (size_t i = 0; i < trace.size(); ++i)
+            fprintf(stderr, "[ssb200]   it %3zu begin %8.3f waited %7.3f queued +%6.3f seen %u known %zu\n", i + 1, trace[i].t_begin,
+                    trace[i].t_wait - trace[i].t_begin, trace[i].t_queued - trace[i].t_wait, trace[i].seen, trace[i].known);
+    }
     for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
     for (uint32_t it = 1; it <= last; ++it) {
         const uint64_t n = (uint64_t)h_counts[it - 1];           // signals that entered iteration `it`
