@@ -131,12 +131,17 @@ public:
             SSB_CUDA(cudaStreamSynchronize(st));
             return;
         }
-        size_t free_b = 0, total_b = 0;
-        SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        const size_t per = ((size_t)N * N + 4 * (size_t)N + Npad + Mp) * sizeof(T);
-        const size_t budget = std::min<size_t>((size_t)(0.6 * (double)free_b) + L_.bytes, (size_t)32 << 30);
-        size_t chunk = std::max<size_t>(1, std::min<size_t>(budget / per, 16384));
-        chunk = std::min(chunk, batch);
+        // (the chunk of the previous call with the same batch is reused: cudaMemGetInfo takes 10-80 ms every few calls on a busy box)
+        size_t chunk = planned_chunk_;
+        if (planned_batch_ != batch || chunk == 0) {
+            size_t free_b = 0, total_b = 0;
+            SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+            const size_t per = ((size_t)N * N + 4 * (size_t)N + Npad + Mp) * sizeof(T);
+            const size_t budget = std::min<size_t>((size_t)(0.6 * (double)free_b) + L_.bytes, (size_t)32 << 30);
+            chunk = std::max<size_t>(1, std::min<size_t>(budget / per, 16384));
+            chunk = std::min(chunk, batch);
+            planned_batch_ = batch; planned_chunk_ = chunk;
+        }
         L_.reserve(chunk * (size_t)N * N * sizeof(T));
         vec_.reserve(chunk * 4 * (size_t)N * sizeof(T));
         S_.reserve(round_up(chunk, 64) * Npad * sizeof(T));
@@ -190,6 +195,7 @@ public:
 
 private:
     dev_buffer Qt_, Rc_, E_, L_, vec_, S_, P_;
+    size_t planned_batch_ = 0, planned_chunk_ = 0;
 };
 
 }  // namespace ssb
