@@ -3,9 +3,11 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config C2]
 
-A step = one pass of the hot path over one batch: every rank solves `batch` signals (C2: 65,536 k=32
-signals against a 512x2048 float32 dictionary).  Weak scaling: per-GPU work is fixed as N grows; the
-dictionary is broadcast once over NCCL, signals are rank-local, reports are gathered each step.
+A step = one pass of the hot path over one batch.  C2 as BASELINE.json states it: 65,536 k=32 signals against a
+512x2048 float32 dictionary, SHARDED over the N GPUs (strong scaling: total work fixed as N grows).  The dictionary
+is broadcast once over NCCL, every rank solves its contiguous slice, and inside the timed region the coefficients --
+in their sparse (index, value, count) form -- and the reports are gathered to rank 0 over NCCL; nothing else is
+exchanged.  --scaling weak keeps `batch` signals per GPU instead (the figure is also added to the strong line as `weak`).
 
   value     signals/s, inputs resident in HBM (device-pointer entry of the C ABI), CUDA-event timed
   e2e       the same through the host-pointer entry: pinned host Y in, host X + reports out, every step
@@ -65,7 +67,11 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true", help="no per-kernel CUDA events in the timed region (roofline absent)")
-    ap.add_argument("--gather-x", action="store_true", help="also gather the dense coefficients to rank 0 each step")
+    ap.add_argument("--gather-x", action="store_true", help="gather the DENSE coefficients instead of the sparse form")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="N > 1: shard the config's batch (strong, default) or keep it per GPU (weak)")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1, strong: do not add the weak-scaling figure")
+    ap.add_argument("--residual", default="auto", choices=["auto", "exact", "incremental"], help="residual-correlation mode of the handle")
+    ap.add_argument("--no-exact-extra", action="store_true", help="do not time the other residual mode as an extra key")
     args = ap.parse_args()
     slow = args.impl == "reference" or CONFIGS[args.config].get("solver") == "irls"
     if args.steps is None:
@@ -100,19 +106,21 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_reference_solve(A, Y, cfg, threads):
+def cpu_reference_solve(A, Y, cfg, threads, full=False):
     """The reference's CPU path on `threads` host threads (one BLAS thread each: its best throughput mode,
-    BASELINE.md §3).  Returns (seconds, kind, iters)."""
+    BASELINE.md §3).  Returns (seconds, kind, iters) (+ X, errs with full=True)."""
     from oracle import ref, port
     if ref.available() and os.path.exists("/root/repo/oracle/_ref/libcblas_fwd.so"):
         ref.set_blas_threads(1)
         t0 = time.perf_counter()
         X, it, err = ref.homotopy(A, Y, cfg["tol"], cfg["max_iter"], threads=threads)
-        return time.perf_counter() - t0, "reference", it
-    os.environ.setdefault("OMP_NUM_THREADS", str(threads))
-    t0 = time.perf_counter()
-    X, it, err = port.homotopy(A, Y, cfg["tol"], cfg["max_iter"])
-    return time.perf_counter() - t0, "port", it
+        secs, kind = time.perf_counter() - t0, "reference"
+    else:
+        os.environ.setdefault("OMP_NUM_THREADS", str(threads))
+        t0 = time.perf_counter()
+        X, it, err = port.homotopy(A, Y, cfg["tol"], cfg["max_iter"])
+        secs, kind = time.perf_counter() - t0, "port"
+    return (secs, kind, it, X, err) if full else (secs, kind, it)
 
 
 class ClockSampler:
@@ -199,9 +207,12 @@ def run_reference(args, cfg):
     line = {
         "impl": "reference", "metric": "homotopy signals/sec", "value": value, "unit": "signals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: homotopy A {cfg['m']}x{cfg['n']} float32, k={cfg['k']}, tol {cfg['tol']}, "
-                               f"max_iter {cfg['max_iter']}", "batch_per_step": sample},
+        "higher_is_better": True, "scaling": "strong" if (args.gpus > 1 and args.scaling == "strong") else "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: homotopy A {cfg['m']}x{cfg['n']} {cfg['dtype']}, {cfg['batch']} k={cfg['k']} signals "
+                               + ("sharded over the GPUs" if (args.gpus > 1 and args.scaling == "strong") else "per GPU")
+                               + f", tol {cfg['tol']}, max_iter {cfg['max_iter']}",
+                   "batch_per_step": sample, "note": "the CPU arm times a bounded sample of the same workload per step"},
         "cpu_baseline": {"value": value, "unit": "signals/s", "cores": threads, "kind": kind,
                          "sample": f"{sample} signals of the {args.config} workload per step, {threads} host threads x 1 BLAS thread"},
         "e2e": {"value": value, "unit": "signals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -376,12 +387,17 @@ def run_b200(args, cfg):
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
-    batch = args.batch or cfg["batch"]
+    total = args.batch or cfg["batch"]
+    strong = world > 1 and args.scaling == "strong"
+    # strong scaling: the config's batch sharded over the ranks (rank g solves signals [lo, hi), its own seeded draw of them);
+    # weak scaling: the config's batch on every rank
+    lo, hi = ssd.shard_bounds(total, world, rank) if strong else (0, total)
+    batch = hi - lo
     dt = np.dtype(cfg["dtype"])
     tdt = torch.float32 if dt == np.float32 else torch.float64
     M, N = cfg["m"], cfg["n"]
 
-    # rank-local signals (weak scaling); the dictionary comes from rank 0 over NCCL
+    # the dictionary comes from rank 0 over NCCL; signals are generated where they are solved
     A, Y = make_workload(cfg, batch, seed=4321 + 1000 * rank)
     if world > 1:
         dA = ssd.broadcast_dictionary(torch.from_numpy(A) if rank == 0 else torch.empty((M, N), dtype=tdt), dist, device=dev)
@@ -398,48 +414,92 @@ def run_b200(args, cfg):
         C.c_void_p(dA.data_ptr()), C.c_size_t(M), C.c_size_t(N), C.c_ssize_t(dA.stride(0)), C.c_ssize_t(dA.stride(1)),
         C.c_int(local), C.byref(solver._h)))
     solver.set_contraction_path(args.path)
-
-    dY = torch.from_numpy(Y).to(dev)
-    dX = torch.empty((batch, N), dtype=tdt, device=dev)
-    dIt = torch.empty(batch, dtype=torch.int32, device=dev)
-    dErr = torch.empty(batch, dtype=torch.float64, device=dev)
+    solver.set_residual_mode(args.residual)
+    residual_mode, coherence = solver.residual_info()
     stream = torch.cuda.current_stream().cuda_stream
+    cap = max(1, min(int(cfg["max_iter"]) + 1, N))       # non-zeros a solution can have: the sparse result's row width
 
-    def step_dev():
-        solver.solve_batch_ptr(dY.data_ptr(), batch, M, dX.data_ptr(), N, dIt.data_ptr(), dErr.data_ptr(),
+    class Buffers:
+        """device buffers of one batch size + the gather targets on rank 0"""
+        def __init__(self, Yh):
+            n = Yh.shape[0]
+            self.n = n
+            self.dY = torch.from_numpy(Yh).to(dev)
+            self.dX = torch.empty((n, N), dtype=tdt, device=dev)
+            self.dIt = torch.empty(n, dtype=torch.int32, device=dev)
+            self.dErr = torch.empty(n, dtype=torch.float64, device=dev)
+            if world > 1:
+                self.idx = torch.empty((n, cap), dtype=torch.int32, device=dev)
+                self.val = torch.empty((n, cap), dtype=tdt, device=dev)
+                self.meta = torch.empty((n, 3), dtype=torch.float64, device=dev)     # count, iterations, solution_error
+                self.cnt = torch.empty(n, dtype=torch.int32, device=dev)
+                mk = (lambda t: [torch.empty_like(t) for _ in range(world)]) if rank == 0 else (lambda t: None)
+                self.g_idx, self.g_val, self.g_meta = mk(self.idx), mk(self.val), mk(self.meta)
+                self.g_X = mk(self.dX) if args.gather_x else None
+
+    def step_dev(B):
+        solver.solve_batch_ptr(B.dY.data_ptr(), B.n, M, B.dX.data_ptr(), N, B.dIt.data_ptr(), B.dErr.data_ptr(),
                                cfg["tol"], cfg["max_iter"], True, stream)
         if world > 1:
-            ssd.gather_reports(dIt, dErr, dist)
+            # results to rank 0 over NCCL: the coefficients in their sparse form ((index, value) x cap + count per signal: a
+            # solution has at most cap = max_iter + 1 non-zeros; 0.65 KB instead of 8 KB per signal at C2) and the reports
             if args.gather_x:
-                ssd.gather_coefficients(dX, dist)
+                dist.gather(B.dX, B.g_X, dst=0)
+            else:
+                check(getattr(lib(), f"ssb200_compress_rows_dev_{solver._sfx}")(
+                    C.c_void_p(B.dX.data_ptr()), C.c_size_t(B.n), C.c_size_t(N), C.c_size_t(N), C.c_size_t(cap),
+                    C.c_void_p(B.idx.data_ptr()), C.c_void_p(B.val.data_ptr()), C.c_void_p(B.cnt.data_ptr()), C.c_int(local),
+                    C.c_void_p(stream)))
+                dist.gather(B.idx, B.g_idx, dst=0)
+                dist.gather(B.val, B.g_val, dst=0)
+            B.meta[:, 0] = B.cnt if not args.gather_x else 0
+            B.meta[:, 1] = B.dIt
+            B.meta[:, 2] = B.dErr
+            dist.gather(B.meta, B.g_meta, dst=0)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(B, steps):
+        """`steps` steps between one pair of CUDA events, barrier + synchronize on both sides; (ms max over ranks, per-step ms)"""
+        barrier()
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        marks[0].record()
+        for i in range(steps):
+            step_dev(B)
+            marks[i + 1].record()
+        barrier()
+        ms = marks[0].elapsed_time(marks[-1])
+        per = [marks[i].elapsed_time(marks[i + 1]) for i in range(steps)]
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t[0].item())
+        return ms, per
+
+    B = Buffers(Y)
+    dY, dX, dIt, dErr = B.dY, B.dX, B.dIt, B.dErr
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     for _ in range(args.warmup):
-        step_dev()
+        step_dev(B)
     # ---- the timed region: K steps, no per-kernel events inside (they cost ~2 ms per step: every record drains the
     # launch pipeline); one event per step boundary only, for the per-step spread
     solver.reset_counters()
     solver.set_timing(False)
-    barrier()
     t_wall0 = time.perf_counter()
-    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    marks[0].record()
-    for i in range(args.steps):
-        step_dev()
-        marks[i + 1].record()
-    barrier()
+    ms, step_ms = timed(B, args.steps)
     if rank == 0:
         sampler.window(t_wall0, time.perf_counter())
-    ms = marks[0].elapsed_time(marks[-1])
-    step_ms = [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)]
     launches_timed = solver.counters()["launches"]
+    gathered = None
+    if world > 1 and rank == 0 and not args.gather_x:      # what rank 0 holds after a step: every rank's reports and sparse rows
+        meta = torch.cat(B.g_meta)
+        gathered = {"signals": int(meta.shape[0]), "mean_iters": float(meta[:, 1].mean().item()),
+                    "nonzeros": int(meta[:, 0].sum().item()), "bytes_per_step": int(sum(t.numel() * t.element_size() for t in B.g_idx + B.g_val + B.g_meta))}
     # ---- the same K steps again with every launch of the lockstep loop bracketed by CUDA events on its stream: the
     # per-kernel durations behind `roofline` / `kernels` (shares are taken against this instrumented pass's own time)
     solver.reset_counters()
@@ -448,7 +508,7 @@ def run_b200(args, cfg):
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     p0.record()
     for _ in range(args.steps):
-        step_dev()
+        step_dev(B)
     p1.record()
     barrier()
     ms_prof = p0.elapsed_time(p1)
@@ -457,6 +517,37 @@ def run_b200(args, cfg):
     counters, timing, prof = solver.counters(), solver.timing(), solver.kernel_profile()
     iters_mean = float(dIt.to(torch.float64).mean().item())
     converged = float((dErr <= cfg["tol"]).to(torch.float64).mean().item())
+    it_default = dIt.cpu().numpy().astype(np.uint32)
+    X_sample = dX[: min(batch, 1024)].cpu().numpy()
+    err_sample = dErr[: min(batch, 1024)].cpu().numpy()
+
+    # ---- the other residual mode on the same inputs (what exactness costs / what the incremental form would give)
+    other = None
+    if not args.no_exact_extra and dt == np.float32:
+        other_mode = "incremental" if residual_mode == "exact" else "exact"
+        solver.set_residual_mode(other_mode)
+        for _ in range(2):
+            step_dev(B)
+        k = max(3, min(args.steps, 10))
+        ms_o, _ = timed(B, k)
+        it_o = dIt.cpu().numpy().astype(np.uint32)
+        other = {"mode": other_mode, "ms_per_step": ms_o / k, "value": world * batch * k / (ms_o * 1e-3), "unit": "signals/s",
+                 "mean_iters": float(it_o.mean()), "iters_equal_to_default_mode": int((it_o == it_default).sum()), "signals": int(batch)}
+        solver.set_residual_mode(args.residual)
+        step_dev(B)                                   # leaves the default mode's results in the buffers
+
+    # ---- weak-scaling figure next to the strong one: the config's whole batch on every GPU
+    weak = None
+    if strong and not args.no_weak:
+        Aw, Yw = make_workload(cfg, total, seed=4321 + 1000 * rank)
+        Bw = Buffers(Yw)
+        for _ in range(2):
+            step_dev(Bw)
+        k = max(3, min(args.steps, 10))
+        ms_w, _ = timed(Bw, k)
+        weak = {"value": world * total * k / (ms_w * 1e-3), "unit": "signals/s", "ms_per_step": ms_w / k, "batch_per_gpu": total,
+                "scaling": "weak", "steps": k}
+        del Bw, Yw
 
     # ---- end to end: pinned host buffers through the host-pointer entry, copies inside the timed region
     e2e = None
@@ -481,9 +572,9 @@ def run_b200(args, cfg):
         h2d_b, d2h_b = solver.transfer_bytes()        # counted by the library from the copies it issues
         assert torch.equal(hIt, dIt.cpu()), "host-pointer and device-pointer entries disagree"
     if world > 1:
-        t = torch.tensor([ms, e2e_s if not args.no_e2e else 0.0], dtype=torch.float64, device=dev)
+        t = torch.tensor([e2e_s if not args.no_e2e else 0.0], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_max = float(t[0].item()), float(t[1].item())
+        e2e_max = float(t[0].item())
     else:
         e2e_max = e2e_s if not args.no_e2e else 0.0
     if not args.no_e2e:
@@ -560,26 +651,42 @@ def run_b200(args, cfg):
              "unit": "TFLOP/s", "note": "whole-solve algorithmic flops 2*M*N*(iters+1) per signal / step time"}
     whole["frac"] = whole["achieved"] / (peak * world)
 
-    cpu = None
+    cpu, parity_block = None, None
     if not args.no_cpu_baseline:
         threads = host_threads()
         sample = args.cpu_sample or (512 if args.config == "C2" else 64)
         sample = min(sample, batch)
-        secs, kind, it_ref = cpu_reference_solve(A, Y[:sample], cfg, threads)
+        secs, kind, it_ref, X_ref, err_ref = cpu_reference_solve(A, Y[:sample], cfg, threads, full=True)
         cpu = {"value": sample / secs, "unit": "signals/s", "cores": threads, "kind": kind,
                "sample": f"first {sample} signals of rank 0's batch, {threads} host threads x 1 BLAS thread, {secs:.1f} s",
-               "iters_match_gpu": int((it_ref == dIt[:sample].cpu().numpy().astype(np.uint32)).sum())}
+               "iters_match_gpu": int((it_ref == it_default[:sample]).sum())}
+        # the parity gate's counts on that sample (tests/parity.py): GPU against the CPU path it is timed beside
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import parity as _parity
+        c0 = np.abs(Y[:sample].astype(np.float64) @ A.astype(np.float64)).max(axis=1)
+        n_par = min(sample, len(X_sample))
+        pc = _parity.counts(_parity.compare(X_sample[:n_par], it_default[:n_par], err_sample[:n_par], X_ref[:n_par], it_ref[:n_par], err_ref[:n_par], c0[:n_par]))
+        parity_block = {"n": pc["n"], "against": kind, "iter": pc["iter"], "support": pc["support"], "soft_support": pc["soft"],
+                        "coef_gt_1e-4": pc["coef"], "coef_max_rel": pc["coef_max"], "solution_error": pc["err"],
+                        "note": "mismatch counts of tests/parity.py on the CPU sample; two CPU builds of the reference show the "
+                                "same classes of rounding-level mismatches against each other (profiles/r2_parity.json)"}
 
     line = {
         "metric": "homotopy signals/sec", "value": world * batch * args.steps / (ms * 1e-3), "unit": "signals/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if dt == np.float32 else "f64",
+        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32" if dt == np.float32 else "f64",
         "data": "synthetic",
-        "config": {"workload": f"{args.config}: homotopy A {M}x{N} {cfg['dtype']}, {batch} k={cfg['k']} signals per GPU, "
-                               f"tol {cfg['tol']}, max_iter {cfg['max_iter']}",
-                   "batch_per_gpu": batch, "mean_iters": iters_mean, "converged_frac": converged,
+        "config": {"workload": f"{args.config}: homotopy A {M}x{N} {cfg['dtype']}, {total} k={cfg['k']} signals "
+                               + ("sharded over the GPUs" if strong else "per GPU") + f", tol {cfg['tol']}, max_iter {cfg['max_iter']}",
+                   "batch_total": world * batch, "batch_per_gpu": batch, "mean_iters": iters_mean, "converged_frac": converged,
                    "l2": "working set (C,Q,X: 3 x %.0f MB per GPU) exceeds the 126 MB L2; no explicit flush" % (batch * N * dt.itemsize / 1e6),
-                   "contraction_path": args.path, "gather_x": bool(args.gather_x)},
+                   "contraction_path": args.path,
+                   "gather": None if world == 1 else ("dense X + reports to rank 0 (NCCL gather), inside the timed region" if args.gather_x else
+                                                      "sparse coefficients ((index, value) x %d + count per signal) + reports to rank 0 (NCCL gather), inside the timed region" % cap)},
+        "residual": {"mode": residual_mode, "requested": args.residual, "mutual_coherence": coherence, "other_mode": other,
+                     "note": "exact = c re-formed from r = y - A_G x_G every iteration (homotopy-cpu.cpp:255); incremental = c -= gamma q; auto "
+                             "takes exact above coherence 0.7 (include/ssb200.h)"},
+        "gathered": gathered, "weak": weak, "parity": parity_block,
         "e2e": e2e, "gpu_launches": launches_timed, "roofline": roofline, "kernels": kernels, "whole_solve": whole,
         "step_ms": {"median": float(np.median(step_ms)), "min": min(step_ms), "max": max(step_ms),
                     "note": "per-step device time inside the timed region (rank 0); `value` uses the whole region"},

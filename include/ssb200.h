@@ -67,9 +67,15 @@ int ssb200_device_count(void);
  * solve_batch: `batch` independent signals, row b of Y at Y + b*ldy (host memory), x_b written
  *   to X + b*ldx (host memory).  New functionality (the reference has no batching, ss.h:50);
  *   each signal's result equals what solve() returns for it.
- * solve_batch_dev: same with DEVICE pointers for Y, X, iters, errors (no host copies);
- *   work is enqueued on `stream` (a cudaStream_t, may be NULL) and the call returns after the
- *   stream has been synchronised.
+ *   A batch row and a solve() of the same signal follow the same algorithm but not the same kernels (one cooperative
+ *   kernel per single solve, SIMT or tcgen05 contraction by batch size), so they agree to rounding, not bit for bit.
+ * solve_batch_dev: same with DEVICE pointers for Y, X, iters, errors (no host copies).  `stream`
+ *   (a cudaStream_t, may be NULL) is the stream the inputs were produced on: it is synchronised
+ *   first, the work then runs on the handle's own streams, and the call returns when the results
+ *   are complete (visible to every stream).
+ * create_dev: the device is synchronised first (dA may come from any stream, e.g. an NCCL broadcast).
+ * max_iterations: any value; the active set holds min(max_iterations + 1, N) atoms and that bound must
+ *   not exceed 4096 (SSB200_INVALID_ARGUMENT otherwise, before any work is queued).
  */
 int ssb200_homotopy_create_f32(const float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
                                int device, void** handle);
@@ -82,6 +88,21 @@ int ssb200_homotopy_create_dev_f64(const double* dA, size_t m, size_t n, ptrdiff
                                    int device, void** handle);
 int ssb200_homotopy_refresh_f32(void* handle, const float* A, ptrdiff_t row_stride, ptrdiff_t col_stride);
 int ssb200_homotopy_refresh_f64(void* handle, const double* A, ptrdiff_t row_stride, ptrdiff_t col_stride);
+
+/* Residual-correlation mode.  The reference re-forms c = A^T (y - A x) from scratch every iteration
+ * (src/solvers/homotopy-cpu.cpp:87-98, called at :215 and :255).
+ *   EXACT        does the same: r = y - A_G x_G is rebuilt from the active atoms every iteration and c = A^T r is contracted
+ *                together with q = A^T (A d) (two contraction rows per signal-iteration).
+ *   INCREMENTAL  carries c -= gamma q from iteration to iteration (one contraction row per signal-iteration).  Algebraically
+ *                the same; on coherent (nearly parallel) dictionaries the rounding drift of c leaves the reference's path
+ *                (more solves run to max_iterations), so it is only taken where it was measured to stay inside the
+ *                reference's own build-to-build noise.
+ *   AUTO         (default) EXACT when the dictionary's mutual coherence max_{i != j} |a_i . a_j| / (|a_i| |a_j|) exceeds 0.7
+ *                (e.g. the reference's bench workload, homotopy_bench.cpp:14-48), INCREMENTAL otherwise.
+ * get_residual_info reports the mode in effect for the handle's dictionary and its mutual coherence. */
+enum { SSB200_RESIDUAL_AUTO = 0, SSB200_RESIDUAL_EXACT = 1, SSB200_RESIDUAL_INCREMENTAL = 2 };
+int ssb200_homotopy_set_residual_mode(void* handle, int mode);
+int ssb200_homotopy_get_residual_info(void* handle, int* mode_in_effect, double* coherence);
 
 int ssb200_homotopy_solve_f32(void* handle, const float* y, ptrdiff_t y_stride, float tolerance, uint32_t max_iterations,
                               float* x, ptrdiff_t x_stride, uint32_t* iter, double* solution_error);
@@ -99,6 +120,33 @@ int ssb200_homotopy_solve_batch_dev_f32(void* handle, const float* dY, size_t ba
 int ssb200_homotopy_solve_batch_dev_f64(void* handle, const double* dY, size_t batch, size_t ldy, double tolerance,
                                         uint32_t max_iterations, double* dX, size_t ldx, uint32_t* d_iters,
                                         double* d_errors, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Multi-GPU group (new: the reference is one signal per call on one CPU, include/ss/ss.h:50).
+ * One process, one communicator over the listed GPUs of the box (ncclCommInitAll), one host thread per GPU.
+ *   create: uploads A to devices[0], replicates it on the others with ONE ncclBroadcast over NVLink, builds a homotopy
+ *     handle per GPU.  NCCL is bound at run time (libnccl.so.2); a one-device group never touches it.
+ *   solve_batch: host pointers, same contract as ssb200_homotopy_solve_batch_*: the batch is cut into ndev contiguous
+ *     shards (the first batch % ndev shards one signal longer), every GPU's thread moves its shard in and out itself.
+ *   solve_batch_dev: dY, dX, d_iters, d_errors live on devices[0] (dense rows: ldy == M, ldx == N when ndev > 1); shards
+ *     are scattered with ncclSend/ncclRecv, solved, and the coefficient rows and reports gathered back the same way.  No
+ *     other collective exists on the path: signals are independent.
+ */
+int ssb200_group_create_f32(const float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                            const int* devices, int ndev, void** group);
+int ssb200_group_create_f64(const double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride,
+                            const int* devices, int ndev, void** group);
+int ssb200_group_solve_batch_f32(void* group, const float* Y, size_t batch, size_t ldy, float tolerance, uint32_t max_iterations,
+                                 float* X, size_t ldx, uint32_t* iters, double* errors);
+int ssb200_group_solve_batch_f64(void* group, const double* Y, size_t batch, size_t ldy, double tolerance, uint32_t max_iterations,
+                                 double* X, size_t ldx, uint32_t* iters, double* errors);
+int ssb200_group_solve_batch_dev_f32(void* group, const float* dY, size_t batch, size_t ldy, float tolerance, uint32_t max_iterations,
+                                     float* dX, size_t ldx, uint32_t* d_iters, double* d_errors, void* stream);
+int ssb200_group_solve_batch_dev_f64(void* group, const double* dY, size_t batch, size_t ldy, double tolerance, uint32_t max_iterations,
+                                     double* dX, size_t ldx, uint32_t* d_iters, double* d_errors, void* stream);
+int ssb200_group_set_residual_mode(void* group, int mode);
+int ssb200_group_size(void* group);
+void ssb200_group_destroy(void* group);
 
 /* ------------------------------------------------------------------------------------------
  * IRLS.  Replaces ss::solver<T, irls_policy>: irls_state(A) = Householder QR of A

@@ -113,3 +113,28 @@ def irls(A, Y, tol, max_iter, threads=1):
     if rc != 0:
         raise RuntimeError("reference irls returned an error")
     return X, iters, errs, spd.astype(bool)
+
+
+def reconstruct_signal(A, x):
+    """Reference ss::reconstruct_signal (include/ss/ss.h:79-86, src/lib.cpp:78-104): y = A x.  A (m, n) row-major."""
+    lib = _load()
+    A = np.ascontiguousarray(A)
+    ct, sfx = _ct(A.dtype)
+    m, n = A.shape
+    x = np.ascontiguousarray(x, dtype=A.dtype)
+    y = np.zeros(m, dtype=A.dtype)
+    fn = getattr(lib, "ssref_reconstruct_" + sfx)
+    fn.restype = None
+    fn(C.c_void_p(A.ctypes.data), C.c_size_t(m), C.c_size_t(n), C.c_void_p(x.ctypes.data), C.c_void_p(y.ctypes.data))
+    return y
+
+
+def norm_l1(A):
+    """Reference ss::norm_l1 (include/ss/ss.h:88-93, src/linalg/norms.h:22-33) on a copy of A; returns the normalised copy."""
+    lib = _load()
+    A = np.array(A, order="C", copy=True)
+    ct, sfx = _ct(A.dtype)
+    fn = getattr(lib, "ssref_norm_l1_" + sfx)
+    fn.restype = None
+    fn(C.c_void_p(A.ctypes.data), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]))
+    return A

@@ -6,6 +6,7 @@
 
 #include "homotopy.cuh"
 #include "irls.cuh"
+#include "group.cuh"
 
 namespace ssb {
 
@@ -96,6 +97,32 @@ static int homotopy_solve_one(void* handle, const T* y, ptrdiff_t ys, T tol, uin
         for (int i = 0; i < h->M; ++i) yy[i] = y[(ptrdiff_t)i * ys];
         h->solve_batch_host(yy.data(), 1, h->M, tol, max_iter, xx.data(), h->N, iter, err);
         for (int j = 0; j < h->N; ++j) x[(ptrdiff_t)j * xs] = xx[j];
+    });
+}
+
+template <typename T>
+static Group<T>* as_group(void* group)
+{
+    SSB_REQUIRE(group, "null group");
+    auto* b = static_cast<GroupBase*>(group);
+    SSB_REQUIRE(b->is_f64 == (sizeof(T) == 8), "group is not of this dtype");
+    return static_cast<Group<T>*>(b);
+}
+
+template <typename T>
+static int group_create(const T* A, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs, const int* devices, int ndev, void** group)
+{
+    return guarded([&] {
+        SSB_REQUIRE(A && devices && group, "null pointer");
+        *group = nullptr;
+        SSB_REQUIRE(ndev >= 1, "a group needs at least one device");
+        for (int i = 0; i < ndev; ++i) require_sm100(devices[i]);
+        int prev = -1;
+        cudaGetDevice(&prev);
+        auto* g = new Group<T>();
+        try { g->create(A, m, n, rs, cs, devices, ndev); } catch (...) { delete g; if (prev >= 0) cudaSetDevice(prev); throw; }
+        if (prev >= 0) cudaSetDevice(prev);
+        *group = static_cast<GroupBase*>(g);
     });
 }
 
@@ -235,6 +262,45 @@ int ssb200_norm_l1_##SFX(T* A, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs, i
 SSB_HOMOTOPY_API(f32, float)
 SSB_HOMOTOPY_API(f64, double)
 
+#define SSB_GROUP_API(SFX, T)                                                                                           \
+int ssb200_group_create_##SFX(const T* A, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs, const int* devices, int ndev, void** g) \
+{ return group_create<T>(A, m, n, rs, cs, devices, ndev, g); }                                                          \
+int ssb200_group_solve_batch_##SFX(void* g, const T* Y, size_t batch, size_t ldy, T tol, uint32_t mi, T* X, size_t ldx,  \
+                                   uint32_t* iters, double* errs)                                                       \
+{ return guarded([&] { auto* s = as_group<T>(g); SSB_REQUIRE(batch == 0 || (Y && X && iters && errs), "null pointer");   \
+                       SSB_REQUIRE(mi > 0, "max_iterations must be positive"); if (batch == 0) return;                  \
+                       int prev = -1; cudaGetDevice(&prev);                                                             \
+                       try { s->solve_batch_host(Y, batch, ldy, tol, mi, X, ldx, iters, errs); }                        \
+                       catch (...) { if (prev >= 0) cudaSetDevice(prev); throw; }                                       \
+                       if (prev >= 0) cudaSetDevice(prev); }); }                                                        \
+int ssb200_group_solve_batch_dev_##SFX(void* g, const T* dY, size_t batch, size_t ldy, T tol, uint32_t mi, T* dX,        \
+                                       size_t ldx, uint32_t* d_iters, double* d_errs, void* stream)                     \
+{ return guarded([&] { auto* s = as_group<T>(g); SSB_REQUIRE(batch == 0 || (dY && dX && d_iters && d_errs), "null pointer"); \
+                       SSB_REQUIRE(mi > 0, "max_iterations must be positive"); if (batch == 0) return;                  \
+                       int prev = -1; cudaGetDevice(&prev);                                                             \
+                       try { s->solve_batch_dev(dY, batch, ldy, tol, mi, dX, ldx, d_iters, d_errs, (cudaStream_t)stream); } \
+                       catch (...) { if (prev >= 0) cudaSetDevice(prev); throw; }                                       \
+                       if (prev >= 0) cudaSetDevice(prev); }); }
+
+SSB_GROUP_API(f32, float)
+SSB_GROUP_API(f64, double)
+
+int ssb200_group_size(void* g)
+{ if (!g) return 0; auto* b = static_cast<GroupBase*>(g);
+  return b->is_f64 ? (int)static_cast<Group<double>*>(b)->devices.size() : (int)static_cast<Group<float>*>(b)->devices.size(); }
+int ssb200_group_set_residual_mode(void* g, int mode)
+{ return guarded([&] { SSB_REQUIRE(g && mode >= 0 && mode <= 2, "bad residual mode"); auto* b = static_cast<GroupBase*>(g);
+                       if (b->is_f64) static_cast<Group<double>*>(b)->set_residual_mode(mode);
+                       else static_cast<Group<float>*>(b)->set_residual_mode(mode); }); }
+void ssb200_group_destroy(void* g)
+{
+    if (!g) return;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    delete static_cast<GroupBase*>(g);
+    if (prev >= 0) cudaSetDevice(prev);
+}
+
 #define SSB_IRLS_API(SFX, T)                                                                                            \
 int ssb200_irls_create_##SFX(const T* A, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs, int device, void** h)          \
 { return irls_create<T>(A, m, n, rs, cs, device, h); }                                                                  \
@@ -284,6 +350,21 @@ int ssb200_get_kernel_bytes(void* h, uint64_t bytes[8])
 int ssb200_get_transfer_bytes(void* h, uint64_t bytes[2])
 { return guarded([&] { SSB_REQUIRE(h && bytes, "null pointer"); auto* b = static_cast<SolverBase*>(h);
                        bytes[0] = b->h2d_bytes.load(); bytes[1] = b->d2h_bytes.load(); }); }
+int ssb200_homotopy_set_residual_mode(void* h, int mode)
+{ return guarded([&] { SSB_REQUIRE(h && mode >= 0 && mode <= 2, "bad residual mode");
+                       auto* b = static_cast<SolverBase*>(h);
+                       SSB_REQUIRE(b->kind == SolverKind::HomotopyF32 || b->kind == SolverKind::HomotopyF64, "handle is not a homotopy solver");
+                       if (b->kind == SolverKind::HomotopyF32) static_cast<Homotopy<float>*>(b)->residual_mode = mode;
+                       else static_cast<Homotopy<double>*>(b)->residual_mode = mode; }); }
+int ssb200_homotopy_get_residual_info(void* h, int* mode_in_effect, double* coherence)
+{ return guarded([&] { SSB_REQUIRE(h, "null handle");
+                       auto* b = static_cast<SolverBase*>(h);
+                       SSB_REQUIRE(b->kind == SolverKind::HomotopyF32 || b->kind == SolverKind::HomotopyF64, "handle is not a homotopy solver");
+                       bool ex; double mu;
+                       if (b->kind == SolverKind::HomotopyF32) { auto* s = static_cast<Homotopy<float>*>(b); ex = s->exact_residual(); mu = s->coherence(); }
+                       else { auto* s = static_cast<Homotopy<double>*>(b); ex = s->exact_residual(); mu = s->coherence(); }
+                       if (mode_in_effect) *mode_in_effect = ex ? SSB200_RESIDUAL_EXACT : SSB200_RESIDUAL_INCREMENTAL;
+                       if (coherence) *coherence = mu; }); }
 int ssb200_set_contraction_path(void* h, int path)
 { return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 3, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
 

@@ -184,10 +184,16 @@ __global__ void __launch_bounds__(THREADS, 1)
 contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                    const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
                    float* __restrict__ Q, int ldq, int rows, int atom_tiles, int sig_tiles, int k_blocks, int tile_sigs,
-                   const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev)
+                   const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev,
+                   int nblk, int blk_off)
 {
     constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;     // operand elements per K-block
     if (rows_dev) { rows = min(rows, *rows_dev); sig_tiles = (rows + tile_sigs - 1) / tile_sigs; }   // host count may be stale (larger)
+    // nblk row blocks of `rows` rows each, blk_off rows apart in P and Q (exact-residual mode: block 0 = P, block 1 = R)
+    const int blk_tiles = sig_tiles;
+    sig_tiles *= nblk;
+    auto tile_row0 = [&](int st) { return (st / blk_tiles) * blk_off + (st % blk_tiles) * tile_sigs; };
+    auto tile_end = [&](int st) { return (st / blk_tiles) * blk_off + rows; };
     extern __shared__ uint8_t smem_raw[];
     constexpr int MAX_STAGES = 8;
     __shared__ __align__(8) uint64_t full_bar[MAX_STAGES], empty_bar[MAX_STAGES], tmem_full_bar, tmem_empty_bar;
@@ -233,7 +239,7 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
             const int part_bytes = part_rows * ROW_BYTES;
             for (int item = cluster_id; item < num_items; item += num_clusters) {
                 const int n0 = ((item % (atom_tiles / cs)) * cs + crank) * TILE_ATOMS;
-                const int r0 = (item / (atom_tiles / cs)) * tile_sigs;
+                const int r0 = tile_row0(item / (atom_tiles / cs));
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
                     const int s = it % nstages;
                     mbar_wait(&empty_bar[s], ((it / nstages) & 1) ^ 1);      // every CTA of the cluster has drained stage s
@@ -288,7 +294,8 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
         uint32_t t = 0;
         for (int item = cluster_id; item < num_items; item += num_clusters, ++t) {
             const int n0 = ((item % (atom_tiles / cs)) * cs + crank) * TILE_ATOMS;
-            const int r0 = (item / (atom_tiles / cs)) * tile_sigs + half * (TILE_SIGS / 2);
+            const int r0 = tile_row0(item / (atom_tiles / cs)) + half * (TILE_SIGS / 2);
+            const int r_end = tile_end(item / (atom_tiles / cs));
             mbar_wait(&tmem_full_bar, t & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
@@ -313,7 +320,7 @@ contract_x3_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_co
 #pragma unroll
             for (int j = 0; j < TILE_SIGS / 2; ++j) {
                 const int rr = r0 + j;
-                if (rr < rows && half * (TILE_SIGS / 2) + j < tile_sigs) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
+                if (rr < r_end && half * (TILE_SIGS / 2) + j < tile_sigs) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
             }
         }
     }
@@ -343,10 +350,16 @@ __global__ void __launch_bounds__(THREADS, 1)
 contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_p_hi, const __grid_constant__ CUtensorMap map_p_lo,
                         float* __restrict__ Q, int ldq, int rows, int atom_pairs, int sig_tiles, int k_blocks,
-                        const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev)
+                        const float* __restrict__ a_inv, const float* __restrict__ p_inv, const int* __restrict__ rows_dev,
+                        int nblk, int blk_off)
 {
     constexpr int KB_ELEMS = F16 ? ROW_BYTES / 2 : ROW_BYTES / 4;
     if (rows_dev) { rows = min(rows, *rows_dev); sig_tiles = (rows + TILE_SIGS - 1) / TILE_SIGS; }
+    // nblk row blocks of `rows` rows each, blk_off rows apart in P and Q (exact-residual mode: block 0 = P, block 1 = R)
+    const int blk_tiles = sig_tiles;
+    sig_tiles *= nblk;
+    auto tile_row0 = [&](int st) { return (st / blk_tiles) * blk_off + (st % blk_tiles) * TILE_SIGS; };
+    auto tile_end = [&](int st) { return (st / blk_tiles) * blk_off + rows; };
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[PAIR_STAGES], empty_bar[PAIR_STAGES], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_slot;
@@ -381,7 +394,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
             uint32_t it = 0;
             for (int item = pair_id; item < num_items; item += num_pairs) {
                 const int n0 = ((item % atom_pairs) * 2 + crank) * TILE_ATOMS;
-                const int r0 = (item / atom_pairs) * TILE_SIGS + crank * PAIR_HALF_SIGS;
+                const int r0 = tile_row0(item / atom_pairs) + crank * PAIR_HALF_SIGS;
                 for (int kb = 0; kb < k_blocks; ++kb, ++it) {
                     const int s = it % PAIR_STAGES;
                     mbar_wait(&empty_bar[s], ((it / PAIR_STAGES) & 1) ^ 1);
@@ -430,7 +443,8 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
         uint32_t t = 0;
         for (int item = pair_id; item < num_items; item += num_pairs, ++t) {
             const int n0 = ((item % atom_pairs) * 2 + crank) * TILE_ATOMS;
-            const int r0 = (item / atom_pairs) * TILE_SIGS + half * (TILE_SIGS / 2);
+            const int r0 = tile_row0(item / atom_pairs) + half * (TILE_SIGS / 2);
+            const int r_end = tile_end(item / atom_pairs);
             mbar_wait(&tmem_full_bar, t & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * (TILE_SIGS / 2));
@@ -454,7 +468,7 @@ contract_x3_pair_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __gr
 #pragma unroll
             for (int j = 0; j < TILE_SIGS / 2; ++j) {
                 const int rr = r0 + j;
-                if (rr < rows && !(dbg & 1)) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
+                if (rr < r_end && !(dbg & 1)) qcol[(size_t)rr * ldq] = F16 ? (r[j] * ainv) * __ldg(p_inv + rr) : r[j];
             }
         }
     }
@@ -506,7 +520,7 @@ CUtensorMap make_map(bool f16, const void* base, int inner, int outer, int box_r
 }
 
 template <bool F16>
-void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev);
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev, int nblk, int blk_off);
 
 }  // namespace
 
@@ -562,7 +576,7 @@ void tc_plan_destroy(TcPlan* p) { delete p; }
 
 namespace {
 template <bool F16>
-void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev)
+void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev, int nblk, int blk_off)
 {
     const int atom_tiles = p->n_pad / TILE_ATOMS;
     const bool thin = rows <= THIN_SIGS;
@@ -577,31 +591,33 @@ void launch(const TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, c
     cfg.attrs = attr; cfg.numAttrs = 1;
     cfg.blockDim = dim3(THREADS); cfg.stream = stream;
     if (!thin && p->pair) {
-        const int atom_pairs = atom_tiles / 2, items = atom_pairs * sig_tiles;
+        const int atom_pairs = atom_tiles / 2, items = atom_pairs * sig_tiles * nblk;
         cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / 2) * 2));
         cfg.dynamicSmemBytes = PAIR_SMEM_BYTES;
         attr[0].val.clusterDim.x = 2;
         SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_pair_kernel<F16>, p->a_hi, p->a_lo, p->p_hi_part[1], p->p_lo_part[1], Q, ldq,
-                                    rows, atom_pairs, sig_tiles, k_blocks, p->a_inv, p->p_inv, rows_dev));
+                                    rows, atom_pairs, sig_tiles, k_blocks, p->a_inv, p->p_inv, rows_dev, nblk, blk_off));
         return;
     }
     const int cs = thin ? 1 : p->cluster, lg = cs == 4 ? 2 : cs == 2 ? 1 : 0;
-    const int items = (atom_tiles / cs) * sig_tiles;
+    const int items = (atom_tiles / cs) * sig_tiles * nblk;
     const CUtensorMap& mh = thin ? p->p_hi_thin : lg ? p->p_hi_part[lg] : p->p_hi;
     const CUtensorMap& ml = thin ? p->p_lo_thin : lg ? p->p_lo_part[lg] : p->p_lo;
     cfg.gridDim = dim3((unsigned)(std::min(items, p->sms / cs) * cs));
     cfg.dynamicSmemBytes = SMEM_BYTES;
     attr[0].val.clusterDim.x = (unsigned)cs;
     SSB_CUDA(cudaLaunchKernelEx(&cfg, contract_x3_kernel<F16>, p->a_hi, p->a_lo, mh, ml, Q, ldq, rows, atom_tiles, sig_tiles,
-                                k_blocks, tile_sigs, p->a_inv, p->p_inv, rows_dev));
+                                k_blocks, tile_sigs, p->a_inv, p->p_inv, rows_dev, nblk, blk_off));
 }
 }  // namespace
 
-void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev)
+void tc_contract(TcPlan* p, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev, int nblk, int blk_off)
 {
     if (rows <= 0) return;
-    SSB_REQUIRE(rows <= p->rows_alloc, "more rows than the plan was built for");
-    if (p->f16) launch<true>(p, rows, Q, ldq, stream, rows_dev); else launch<false>(p, rows, Q, ldq, stream, rows_dev);
+    SSB_REQUIRE(nblk >= 1 && (nblk - 1) * blk_off + rows <= p->rows_alloc, "more rows than the plan was built for");
+    SSB_REQUIRE(nblk == 1 || blk_off % TILE_SIGS == 0, "row blocks must start on a tile boundary");
+    if (p->f16) launch<true>(p, rows, Q, ldq, stream, rows_dev, nblk, blk_off);
+    else launch<false>(p, rows, Q, ldq, stream, rows_dev, nblk, blk_off);
 }
 
 }  // namespace ssb

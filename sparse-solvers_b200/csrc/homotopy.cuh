@@ -68,6 +68,26 @@ __global__ void f16_split_kernel(const float* __restrict__ src, __half* __restri
     }
 }
 
+// mutual coherence of the dictionary from its Gram matrix: max_{i != j} |G_ij| / sqrt(G_ii G_jj) (positive floats order as
+// unsigned integers).  Decides the residual mode and whether q may be formed from rows of G (Homotopy::exact_residual).
+template <typename T>
+__global__ void coherence_kernel(const T* __restrict__ G, int ldg, int N, unsigned int* __restrict__ mu_bits)
+{
+    float mx = 0.f;
+    const size_t total = (size_t)N * N;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(e / N), j = (int)(e % N);
+        if (i == j) continue;
+        const double gii = (double)G[(size_t)i * ldg + i], gjj = (double)G[(size_t)j * ldg + j];
+        if (gii > 0.0 && gjj > 0.0) {
+            const float v = (float)(fabs((double)G[(size_t)i * ldg + j]) / sqrt(gii * gjj));
+            if (v < FLT_MAX) mx = fmaxf(mx, v);
+        }
+    }
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0 && mx > 0.f) atomicMax(mu_bits, __float_as_uint(mx));
+}
+
 // Y[b][m] = sum_n A[m][n] X[b][n]   (ss::reconstruct_signal, src/lib.cpp:78-104), one CTA per signal
 template <typename T>
 __global__ void __launch_bounds__(128)
@@ -116,6 +136,9 @@ class Homotopy : public SolverBase {
 public:
     static constexpr int STEP_THREADS = 128;
     static constexpr int MAX_LANES = 2;
+    // the lockstep loop runs at most MAX_RUN_AHEAD iterations ahead of the newest signal count the host has seen; the
+    // per-iteration counts live in a ring of that many slots + 2 (any max_iterations, no per-call allocation)
+    static constexpr uint32_t MAX_RUN_AHEAD = 64, COUNT_RING = MAX_RUN_AHEAD + 2;
 
     Homotopy(int dev)
         : SolverBase(sizeof(T) == 4 ? SolverKind::HomotopyF32 : SolverKind::HomotopyF64, dev) {}
@@ -139,6 +162,9 @@ public:
     // A already on this device
     void set_dictionary_dev(const T* dA, size_t m, size_t n, ptrdiff_t rs, ptrdiff_t cs) {
         check_shape(m, n);
+        // dA may have been produced on any stream of this device (an NCCL broadcast on torch's stream, a pageable upload):
+        // the create call has no stream argument, so everything queued on the device so far is waited for
+        SSB_CUDA(cudaDeviceSynchronize());
         alloc_dictionary();
         pack_dictionary_kernel<T><<<1024, 256, 0, stream>>>(dA, (long long)rs, (long long)cs, M, N, At_, Mp, Npad);
         SSB_CUDA(cudaGetLastError());
@@ -156,13 +182,30 @@ public:
     // returns the mean device time per launch in ms
     double debug_contract(const T* P, size_t rows, T* Q, int path, int reps);
 
+    // How the residual correlation c = A^T (y - A x) (homotopy-cpu.cpp:87-98, re-formed at :255 every iteration) is kept:
+    //   exact        r = y - A_G x_G re-formed every iteration and contracted next to the direction (kernel header of
+    //                homotopy_kernels.cuh): the reference's own numerics, two contraction rows per signal-iteration
+    //   incremental  c -= gamma q: one contraction row per signal-iteration; drifts on coherent dictionaries
+    // mode 0 (auto) takes the exact form whenever the dictionary's mutual coherence exceeds COHERENCE_LIMIT -- the regime
+    // where the incremental form was measured to leave the reference's path (tests/studies, profiles/r2_parity.json);
+    // SSB200_RESIDUAL=exact|incremental overrides an `auto` handle (A/B runs).
+    static constexpr float COHERENCE_LIMIT = 0.7f;
+    int residual_mode = 0;               // 0 auto, 1 exact, 2 incremental
+    float coherence() const { return coherence_; }
+    bool coherent() const { return !(coherence_ <= COHERENCE_LIMIT); }
+    bool exact_residual() const {
+        int mode = residual_mode;
+        if (mode == 0) if (const char* e = getenv("SSB200_RESIDUAL")) mode = e[0] == 'e' ? 1 : e[0] == 'i' ? 2 : 0;
+        return mode == 1 || (mode == 0 && coherent());
+    }
+
 private:
     // One lane = one sub-batch in flight: its own stream and workspace.  Two lanes run concurrently so that one
     // lane's tensor-bound contraction overlaps the other's HBM/latency-bound step kernel (and, on the host-pointer
     // path, its H2D / D2H copies).
     struct Lane {
         cudaStream_t stream = nullptr;
-        dev_buffer C, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, mask, act[2], counts;
+        dev_buffer C, C0, Q, P[2], Plo[2], Pinv[2], gam, dG, Ginv, lam, K, pick, mask, act[2], counts, ymax;
         // host-pointer entry: double-buffered staging and the stream its copy-outs run on
         dev_buffer stY[2], stX[2], stIt[2], stErr[2];
         // ... sparse return: the coefficients travel as (index, value) x Kmax + count per signal and are scattered into the
@@ -178,6 +221,7 @@ private:
         bool plan_f16 = false;            // container flavour the plans were built for
         size_t ws_rows = 0;
         int ws_kmax = 0;
+        int ws_nb = 1;                    // row blocks of P and Q: 2 in exact-residual mode (directions | residuals)
         // instrumentation, merged into the handle after the solve
         uint64_t counters[4] = { 0, 0, 0, 0 };
         uint64_t rows[6] = { 0, 0, 0, 0, 0, 0 };   // signal-rows per launch class (SolverBase::kernel_rows)
@@ -211,13 +255,14 @@ private:
             return (int)spans.size() - 1;
         }
         void end(int id) { if (id >= 0) SSB_CUDA(cudaEventRecord(spans[id].b, stream)); }
-        size_t ws_bytes() const { return C.bytes + Q.bytes + P[0].bytes + P[1].bytes + Plo[0].bytes + Plo[1].bytes + Ginv.bytes; }
+        size_t ws_bytes() const { return C.bytes + C0.bytes + Q.bytes + P[0].bytes + P[1].bytes + Plo[0].bytes + Plo[1].bytes + Ginv.bytes; }
     };
 
     dev_buffer dict_;                 // At | At_hi | At_lo | G in one slab (one L2 persistence window covers it)
     T* At_ = nullptr; T* At_hi_ = nullptr; T* At_lo_ = nullptr; T* G_ = nullptr;
     __half* At16_hi_ = nullptr; __half* At16_lo_ = nullptr; float* a_inv_ = nullptr; unsigned int* amax_bits_ = nullptr;
     float amax_ = 0.f;
+    float coherence_ = 0.f;
     std::vector<std::unique_ptr<Lane>> lanes_;
     std::mutex merge_mu_;
     size_t l2_set_aside_ = 0;
@@ -234,7 +279,7 @@ private:
         const size_t a = (size_t)Npad * Mp, g = (size_t)Npad * Npad;
         // float32: At | tf32 hi | tf32 lo | fp16 (hi, lo) | G | a_inv | amax ; float64: At | G
         const size_t parts = sizeof(T) == 4 ? 4 : 1;
-        const size_t extra = sizeof(T) == 4 ? (size_t)Npad + 4 : 0;
+        const size_t extra = sizeof(T) == 4 ? (size_t)Npad + 4 : 4;   // + a_inv (float32) + amax / coherence bits
         dict_.reserve((parts * a + g + extra) * sizeof(T));
         At_ = dict_.as<T>();
         At_hi_ = sizeof(T) == 4 ? At_ + a : nullptr;
@@ -245,6 +290,8 @@ private:
             At16_lo_ = At16_hi_ + a;
             a_inv_ = reinterpret_cast<float*>(G_ + g);
             amax_bits_ = reinterpret_cast<unsigned int*>(a_inv_ + Npad);
+        } else {
+            amax_bits_ = reinterpret_cast<unsigned int*>(G_ + g);
         }
     }
     void finish_dictionary();
@@ -255,9 +302,10 @@ private:
     void apply_l2_policy(cudaStream_t st);
 
     struct plan_key {
-        size_t batch; int kmax; bool host_path; int env_lanes, env_chunk;
+        size_t batch; int kmax; bool host_path; int env_lanes, env_chunk; bool exact;
         bool operator==(const plan_key& o) const {
-            return batch == o.batch && kmax == o.kmax && host_path == o.host_path && env_lanes == o.env_lanes && env_chunk == o.env_chunk;
+            return batch == o.batch && kmax == o.kmax && host_path == o.host_path && env_lanes == o.env_lanes && env_chunk == o.env_chunk &&
+                   exact == o.exact;
         }
     };
     plan_key plan_key_{};
@@ -265,12 +313,15 @@ private:
     int plan_lanes_ = 0;
     bool plan_valid_ = false;
 
-    size_t bytes_per_signal(int kmax) const {
-        return (size_t)(2 * Npad + 4 * Mp + (size_t)kmax * kmax + 2 * kmax + 4) * sizeof(T) + 6 * sizeof(int);
+    size_t bytes_per_signal(int kmax) const {   // exact mode: Q and the right-hand sides twice, c0 kept
+        const size_t nb = exact_residual() ? 2 : 1;
+        return (size_t)((1 + nb + (nb - 1)) * Npad + 4 * nb * Mp + (size_t)kmax * kmax + 2 * kmax + 4) * sizeof(T) + 6 * sizeof(int);
     }
     // signals per chunk and number of lanes for a batch
     void plan_batch(size_t batch, int kmax, bool host_path, size_t& chunk, int& nlanes);
     void reserve_workspace(Lane& L, size_t rows, int kmax);
+    static int active_set_capacity(uint32_t max_iter, int n) { return (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)n); }
+    void check_capacity(int kmax) const;
     bool use_tc(size_t rows) const {
         if (sizeof(T) != 4) return false;
         if (contraction_path == 1) return false;
@@ -284,7 +335,7 @@ private:
         if (const char* e = getenv("SSB200_TF32")) if (atoi(e) != 0) return false;   // tuning knob
         return true;
     }
-    void contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev = nullptr, bool count_rows = false);
+    void contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev = nullptr, bool count_rows = false, int nblk = 1);
     void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                      uint32_t* d_iters, double* d_errs);
     void merge(Lane& L);

@@ -21,8 +21,33 @@ void Homotopy<T>::finish_dictionary()
         SSB_CUDA(cudaMemcpyAsync(&amax_, amax_bits_, sizeof(float), cudaMemcpyDeviceToHost, stream));
         counters[0] += 2;
     }
+    // mutual coherence (from G): which residual form and whether the Gram shortcut may be used (exact_residual())
+    SSB_CUDA(cudaMemsetAsync(amax_bits_ + 1, 0, sizeof(unsigned int), stream));
+    coherence_kernel<T><<<512, 256, 0, stream>>>(G_, Npad, N, amax_bits_ + 1);
+    SSB_CUDA(cudaGetLastError());
+    SSB_CUDA(cudaMemcpyAsync(&coherence_, amax_bits_ + 1, sizeof(float), cudaMemcpyDeviceToHost, stream));
+    counters[0]++;
     SSB_CUDA(cudaStreamSynchronize(stream));
     for (auto& l : lanes_) l->drop_plans();
+    plan_valid_ = false;
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE attribute: one bit per device and kernel instantiation
+static inline void optin_shared_memory(const void* fn, std::atomic<uint64_t>& done)
+{
+    int dev = 0;
+    SSB_CUDA(cudaGetDevice(&dev));
+    const uint64_t bit = 1ull << (dev & 63);
+    if (dev < 64 && (done.load(std::memory_order_acquire) & bit)) return;
+    SSB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    done.fetch_or(bit, std::memory_order_release);
+}
+
+template <typename T>
+void Homotopy<T>::check_capacity(int kmax) const
+{
+    // the step kernel keeps up to 16 active-set slots per thread of 256 (launch_step: SSB_STEP_BIG)
+    SSB_REQUIRE(kmax <= 16 * 256, "max_iterations too large: the active set is limited to 4096 atoms (min(max_iterations + 1, N))");
 }
 
 // marks the dictionary slab as persisting in L2 for work on `st` (c, q, P, Ginv traffic is streaming)
@@ -54,7 +79,7 @@ void Homotopy<T>::plan_batch(size_t batch, int kmax, bool host_path, size_t& chu
     // the plan of the previous call with the same shape is reused: cudaMemGetInfo goes through the resource manager and was
     // measured to take 10-80 ms every few calls on a busy box (tools/variance.py: the only slow part of a slow step)
     const char* env_l = getenv("SSB200_LANES"); const char* env_c = getenv("SSB200_CHUNK");
-    const plan_key key{ batch, kmax, host_path, env_l ? atoi(env_l) : -1, env_c ? atoi(env_c) : -1 };
+    const plan_key key{ batch, kmax, host_path, env_l ? atoi(env_l) : -1, env_c ? atoi(env_c) : -1, exact_residual() };
     if (plan_valid_ && key == plan_key_) { chunk = plan_chunk_; nlanes = plan_lanes_; return; }
     size_t free_b = 0, total_b = 0;
     SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -85,23 +110,26 @@ template <typename T>
 void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
 {
     const size_t rows_alloc = round_up(rows, 256);
-    if (rows_alloc <= L.ws_rows && kmax <= L.ws_kmax) return;
+    const int nb = exact_residual() ? 2 : 1;       // exact mode: a block of residual rows behind the direction rows
+    if (rows_alloc <= L.ws_rows && kmax <= L.ws_kmax && nb == L.ws_nb) return;
     const size_t r = std::max(rows_alloc, L.ws_rows);
     const int k = std::max(kmax, L.ws_kmax);
     L.drop_plans();
     L.C.reserve(r * Npad * sizeof(T));
-    L.Q.reserve(r * Npad * sizeof(T));
+    if (nb == 2) L.C0.reserve(r * Npad * sizeof(T));
+    L.Q.reserve(nb * r * Npad * sizeof(T));
     for (int i = 0; i < 2; ++i) {
-        const bool grew = L.P[i].bytes < r * Mp * sizeof(T);
-        L.P[i].reserve(r * Mp * sizeof(T));
+        const size_t want = nb * r * Mp * sizeof(T);
+        const bool grew = L.P[i].bytes < want;
+        L.P[i].reserve(want);
         if (grew) SSB_CUDA(cudaMemsetAsync(L.P[i].p, 0, L.P[i].bytes, L.stream));   // rows past `count` feed the tensor tiles
         if (sizeof(T) == 4) {
-            const bool grew_lo = L.Plo[i].bytes < r * Mp * sizeof(T);
-            L.Plo[i].reserve(r * Mp * sizeof(T));
+            const bool grew_lo = L.Plo[i].bytes < want;
+            L.Plo[i].reserve(want);
             if (grew_lo) SSB_CUDA(cudaMemsetAsync(L.Plo[i].p, 0, L.Plo[i].bytes, L.stream));
         }
         L.act[i].reserve(r * sizeof(int));
-        L.Pinv[i].reserve(r * sizeof(float));
+        L.Pinv[i].reserve(nb * r * sizeof(float));
     }
     L.gam.reserve(r * k * sizeof(uint32_t));
     L.dG.reserve(r * k * sizeof(T));
@@ -110,19 +138,22 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
     L.K.reserve(r * sizeof(int));
     L.pick.reserve(r * sizeof(uint32_t));
     L.mask.reserve(r * (size_t)(Npad / 32) * sizeof(uint32_t));
-    L.counts.reserve(4096 * sizeof(int));
-    L.h_count.reserve(4096 * sizeof(int));
+    L.ymax.reserve(r * sizeof(float));
+    L.counts.reserve(COUNT_RING * sizeof(int));
+    L.h_count.reserve(COUNT_RING * sizeof(int));
     SSB_CUDA(cudaStreamSynchronize(L.stream));
     L.ws_rows = r;
     L.ws_kmax = k;
+    L.ws_nb = nb;
     apply_l2_policy(L.stream);
 }
 
-// Q[r][:] = A^T P[which][r][:] for r < rows
+// Q[b * ws_rows + r][:] = A^T P[which][b * ws_rows + r][:] for r < rows, b < nblk (block 0: directions, block 1: residuals)
 template <typename T>
-void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev, bool count_rows)
+void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev, bool count_rows, int nblk)
 {
     const int span = L.begin(timing, 0);
+    const size_t prow = (size_t)L.ws_nb * L.ws_rows;          // rows of the P buffers
     if constexpr (sizeof(T) == 4) {
         if (tc) {
             const bool f16 = use_f16();
@@ -130,23 +161,24 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* 
             if (!L.plan[which]) {
                 if (f16) {
                     __half* hi = L.Plo[which].template as<__half>();
-                    L.plan[which] = tc_plan_create(true, At16_hi_, At16_lo_, Npad, Mp, hi, hi + L.ws_rows * Mp, (int)L.ws_rows,
+                    L.plan[which] = tc_plan_create(true, At16_hi_, At16_lo_, Npad, Mp, hi, hi + prow * Mp, (int)prow,
                                                    a_inv_, L.Pinv[which].template as<float>());
                 } else {
-                    L.plan[which] = tc_plan_create(false, At_hi_, At_lo_, Npad, Mp, L.P[which].p, L.Plo[which].p, (int)L.ws_rows,
+                    L.plan[which] = tc_plan_create(false, At_hi_, At_lo_, Npad, Mp, L.P[which].p, L.Plo[which].p, (int)prow,
                                                    nullptr, nullptr);
                 }
             }
-            tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream, rows_dev);
+            tc_contract(L.plan[which], (int)rows, L.Q.template as<float>(), Npad, L.stream, rows_dev, nblk, (int)L.ws_rows);
             L.counters[0]++;
         }
     }
     if (!tc)
-        L.counters[0] += launch_contract_simt<T>(At_, Mp, Npad, Mp, L.P[which].template as<T>(), Mp, (int)rows,
-                                                 L.Q.template as<T>(), Npad, L.stream);
+        for (int b = 0; b < nblk; ++b)
+            L.counters[0] += launch_contract_simt<T>(At_, Mp, Npad, Mp, L.P[which].template as<T>() + (size_t)b * L.ws_rows * Mp, Mp, (int)rows,
+                                                     L.Q.template as<T>() + (size_t)b * L.ws_rows * Npad, Npad, L.stream);
     L.end(span);
     L.counters[1]++;
-    if (count_rows) L.counters[2] += rows;
+    if (count_rows) L.counters[2] += (uint64_t)nblk * rows;
 }
 
 
@@ -155,11 +187,8 @@ constexpr int STEP_KR = 3, STEP_KR_BIG = 16;   // active-set slots per thread of
 template <typename T, int THREADS, int NCH, bool GS, int KR = STEP_KR>
 static void launch_step_variant(unsigned grid, size_t smem, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
-    static size_t configured = 0;   // per process; one device per process in every supported deployment
-    if (smem > 48 * 1024 && smem > configured) {
-        SSB_CUDA(cudaFuncSetAttribute(homotopy_step_kernel<T, THREADS, NCH, GS, KR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = 200 * 1024;
-    }
+    static std::atomic<uint64_t> configured{ 0 };
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_step_kernel<T, THREADS, NCH, GS, KR>, configured);
     homotopy_step_kernel<T, THREADS, NCH, GS, KR><<<grid, THREADS, smem, st>>>(a, kb, ks);
     SSB_CUDA(cudaGetLastError());
 }
@@ -203,12 +232,9 @@ static void launch_scan(int threads, int nch, bool gram, unsigned grid, cudaStre
 template <typename T, int W>
 static void launch_algebra_variant(unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
-    static size_t configured = 0;
+    static std::atomic<uint64_t> configured{ 0 };
     const size_t smem = slice * W;
-    if (smem > 48 * 1024 && smem > configured) {
-        SSB_CUDA(cudaFuncSetAttribute(homotopy_algebra_kernel<T, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = 200 * 1024;
-    }
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_algebra_kernel<T, W>, configured);
     homotopy_algebra_kernel<T, W><<<(rows + W - 1) / W, W * 32, smem, st>>>(a, kb, ks, (int)slice);
     SSB_CUDA(cudaGetLastError());
 }
@@ -238,6 +264,9 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
 {
     cudaStream_t st = L.stream;
     const bool tc = use_tc(rows);
+    const bool exact = L.ws_nb == 2;                   // reserve_workspace sized the row blocks from exact_residual()
+    const size_t boff = L.ws_rows;                     // rows between the direction block and the residual block
+    const size_t prow = (size_t)L.ws_nb * L.ws_rows;
     HomArgs<T> a{};
     a.N = N; a.ldc = Npad; a.Mp = Mp; a.ldp = Mp; a.Kmax = L.ws_kmax;
     a.At = At_; a.G = G_; a.ldg = Npad;
@@ -245,44 +274,35 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     a.gam = L.gam.template as<uint32_t>(); a.dG = L.dG.template as<T>(); a.Ginv = L.Ginv.template as<T>();
     a.lam = L.lam.template as<T>(); a.Kcur = L.K.template as<int>(); a.pick = L.pick.template as<uint32_t>(); a.mask = L.mask.template as<uint32_t>();
     a.iters = d_iters; a.errs = d_errs;
+    a.exact = exact ? 1 : 0;
+    a.Qc = exact ? L.Q.template as<T>() + boff * Npad : nullptr;
+    a.Y = dY; a.ldy = ldy; a.M = M; a.ymax = L.ymax.template as<float>();
     const int tc_split = tc ? (use_f16() ? 2 : 1) : 0;
     a.split = tc_split;
     a.amax = amax_;
-    // where right-hand sides number i go for the current split (hi / full, lo, inverse scales)
+    // where right-hand sides number i go for the current split (hi / full, lo, inverse scales); exact mode: the residual
+    // rows of the same buffers, one block (ws_rows rows) further
     auto set_rhs = [&](int i, int split) {
         if (split == 2) {
             __half* hi = L.Plo[i].template as<__half>();
+            __half* lo = hi + prow * Mp;
             a.Pn = reinterpret_cast<T*>(hi);
-            a.Pn_lo = reinterpret_cast<T*>(hi + L.ws_rows * Mp);
+            a.Pn_lo = reinterpret_cast<T*>(lo);
             a.Pn_inv = L.Pinv[i].template as<float>();
+            a.Rn = reinterpret_cast<T*>(hi + boff * Mp);
+            a.Rn_lo = reinterpret_cast<T*>(lo + boff * Mp);
+            a.Rn_inv = a.Pn_inv + boff;
         } else {
             a.Pn = L.P[i].template as<T>();
             a.Pn_lo = split ? L.Plo[i].template as<T>() : nullptr;
             a.Pn_inv = nullptr;
+            a.Rn = a.Pn + boff * Mp;
+            a.Rn_lo = split ? a.Pn_lo + boff * Mp : nullptr;
+            a.Rn_inv = nullptr;
         }
     };
     a.tol = tol; a.max_iter = max_iter;
     if (const char* e = getenv("SSB200_DBG")) a.dbg = atoi(e);
-
-    // c0 = A^T y for the whole chunk (homotopy-cpu.cpp:215)
-    {
-        set_rhs(0, a.split);
-        const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
-        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, a.Pn, a.Pn_lo, a.Pn_inv, Mp, a.split);
-        SSB_CUDA(cudaGetLastError());
-        L.counters[0]++;
-    }
-    contract(L, tc, 0, rows, nullptr, true);
-    {
-        a.act = nullptr; a.act_next = nullptr; a.next_count = nullptr;
-        set_rhs(1, a.split);
-        a.it = 0;
-        const int span = L.begin(timing, 1);
-        homotopy_init_kernel<T, STEP_THREADS><<<(unsigned)rows, STEP_THREADS, 0, st>>>(a);
-        SSB_CUDA(cudaGetLastError());
-        L.end(span);
-        L.counters[0]++;
-    }
 
     // step-kernel variant: c,q register-resident when the dictionary is narrow enough, inverse on chip when it fits
     constexpr int V = 16 / sizeof(T);
@@ -296,27 +316,57 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     const size_t g_budget = 96 * 1024;
     bool split_ok = true;                                                                            // scan + algebra kernels
     if (const char* e = getenv("SSB200_SPLIT")) split_ok = atoi(e) != 0;                              // tuning knob
+    uint32_t RUN_AHEAD = 8;
+    if (const char* e = getenv("SSB200_RUN_AHEAD")) RUN_AHEAD = (uint32_t)std::max(1, std::min((int)MAX_RUN_AHEAD, atoi(e)));   // tuning knob
+    // While the active set is small (K <= it < gram_iters) q = G[:, active] d -- and, in exact mode, c' = A^T y - G[:, active] x
+    // from the same rows -- costs K rows of G per signal in the scan kernel: less than a contraction, a K-atom gather and the Q
+    // traffic.  Sums over rows of G cancel badly when the atoms are nearly parallel (measured: tests/studies/residual_modes.py,
+    // "Gram form"), so coherent dictionaries do not take this route.
+    uint32_t gram_iters = 16;                                    // iterations 1 .. gram_iters - 1 take q from the Gram matrix
+    if (const char* e = getenv("SSB200_GRAM_ITERS")) gram_iters = (uint32_t)std::max(0, std::min(32, atoi(e)));   // tuning knob
+    if (!split_ok || nch == 0 || coherent() || algebra_warps(homotopy_algebra_slice<T>((int)gram_iters, ((int)gram_iters + 1) | 1)) == 0) gram_iters = 0;
+    gram_iters = std::min<uint32_t>(gram_iters, (uint32_t)L.ws_kmax);
+    a.C0 = (exact && gram_iters > 1) ? L.C0.template as<T>() : nullptr;
 
-    // Lockstep loop.  The number of signals still running lives on the device: counts[it] is appended to by iteration
-    // it and read by iteration it + 1 (every kernel bounds itself by it), so the host never has to wait for an
-    // iteration before queueing the next.  The read-backs travel on a side stream: behind another lane's bulk copy-out a
-    // 4-byte copy can wait milliseconds, and on the main stream that wait would stall the kernels behind it.  It reads the counts back asynchronously, sizes the grids from the newest one
-    // it has (counts only fall, so a stale one is a valid upper bound), and stays at most RUN_AHEAD iterations ahead.
+    // c0 = A^T y for the whole chunk (homotopy-cpu.cpp:215)
+    {
+        set_rhs(0, a.split);
+        const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
+        stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY, ldy, M, (int)rows, a.Pn, a.Pn_lo, a.Pn_inv, Mp, a.split,
+                                                        L.ymax.template as<float>());
+        SSB_CUDA(cudaGetLastError());
+        L.counters[0]++;
+    }
+    contract(L, tc, 0, rows, nullptr, true);
+    {
+        a.act = nullptr; a.act_next = nullptr; a.next_count = nullptr; a.count_zero = nullptr;
+        set_rhs(1, a.split);
+        a.it = 0;
+        const int span = L.begin(timing, 1);
+        homotopy_init_kernel<T, STEP_THREADS><<<(unsigned)rows, STEP_THREADS, 0, st>>>(a);
+        SSB_CUDA(cudaGetLastError());
+        L.end(span);
+        L.counters[0]++;
+    }
+
+    // Lockstep loop.  The number of signals still running lives on the device: the count of iteration `it` is appended to by
+    // iteration it and read by iteration it + 1 (every kernel bounds itself by it), so the host never has to wait for an
+    // iteration before queueing the next.  The counts sit in a ring of COUNT_RING slots (any max_iterations): iteration it
+    // clears the slot iteration it + 1 will append to -- its previous occupant, COUNT_RING iterations older, has been read by
+    // its kernels and copied to the host long before, because the host stays at most RUN_AHEAD < COUNT_RING - 1 iterations
+    // ahead of the newest count it has seen.  The read-backs travel on a side stream: behind another lane's bulk copy-out a
+    // 4-byte copy can wait milliseconds, and on the main stream that wait would stall the kernels behind it.  Grids are
+    // sized from the newest count the host has (counts only fall, so a stale one is a valid upper bound).
     // The SIMT contraction takes its row count on the host, so that path waits for every iteration.
     int sync_iters = 0;
     if (const char* e = getenv("SSB200_SYNC_ITERS")) sync_iters = atoi(e);                            // debugging aid
-    uint32_t RUN_AHEAD = 8;
-    if (const char* e = getenv("SSB200_RUN_AHEAD")) RUN_AHEAD = (uint32_t)std::max(1, std::min(64, atoi(e)));   // tuning knob
-    uint32_t gram_iters = 16;                                    // iterations 1 .. gram_iters - 1 take q from the Gram matrix
-    if (const char* e = getenv("SSB200_GRAM_ITERS")) gram_iters = (uint32_t)std::max(0, std::min(32, atoi(e)));   // tuning knob
-    if (!split_ok || nch == 0 || algebra_warps(homotopy_algebra_slice<T>((int)gram_iters, ((int)gram_iters + 1) | 1)) == 0) gram_iters = 0;
-    gram_iters = std::min<uint32_t>(gram_iters, (uint32_t)L.ws_kmax);
     int cur = 1;                 // P[cur] holds the right-hand sides of this iteration
-    int* d_counts = L.counts.template as<int>();        // [max_iter + 2]
-    int* h_counts = L.h_count.template as<int>();       // pinned mirror
-    SSB_CUDA(cudaMemsetAsync(d_counts, 0, ((size_t)max_iter + 2) * sizeof(int), st));
-    h_counts[0] = (int)rows;
-    SSB_CUDA(cudaMemcpyAsync(d_counts, h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+    int* d_counts = L.counts.template as<int>();        // [COUNT_RING]
+    int* h_ring = L.h_count.template as<int>();         // pinned mirror
+    auto slot = [](uint32_t i) { return i % COUNT_RING; };
+    SSB_CUDA(cudaMemsetAsync(d_counts, 0, COUNT_RING * sizeof(int), st));
+    h_ring[0] = (int)rows;
+    SSB_CUDA(cudaMemcpyAsync(d_counts, h_ring, sizeof(int), cudaMemcpyHostToDevice, st));
     while (L.count_events.size() < RUN_AHEAD + 1) {
         cudaEvent_t e, f;
         SSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); L.count_events.push_back(e);
@@ -325,9 +375,10 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     if (!L.side) SSB_CUDA(cudaStreamCreateWithFlags(&L.side, cudaStreamNonBlocking));
     const bool async = tc;
     size_t known = rows;         // newest count the host has seen (upper bound of the current one)
-    uint32_t seen = 0;           // ... which is counts[seen]
+    uint32_t seen = 0;           // ... which is the count of iteration `seen`
     uint32_t last = 0;
-    std::vector<uint8_t> route((size_t)max_iter + 2, 0);   // launch class of every iteration's scan (kernel profile)
+    std::vector<int> hist{ (int)rows };                    // hist[j] = signals that continue after iteration j
+    std::vector<uint8_t> route{ 0 };                        // launch class of every iteration's scan (kernel profile)
     // debugging aid (SSB200_TRACE_STALL=<ms>): host timeline of a chunk that took longer than <ms> -- when each iteration was
     // queued, how long the host waited for a count, which count it had then
     double trace_ms = 0.0;
@@ -338,28 +389,27 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_chunk0).count(); };
     for (uint32_t it = 1; it <= max_iter; ++it) {
         const double t_begin = trace_ms > 0 ? now_ms() : 0.0;
-        const uint32_t must = async ? (it > RUN_AHEAD ? it - RUN_AHEAD : 0) : it - 1;   // counts[must] has to be in
+        const uint32_t must = async ? (it > RUN_AHEAD ? it - RUN_AHEAD : 0) : it - 1;   // this iteration's count has to be in
         for (uint32_t j = seen + 1; j < it; ++j) {
             cudaEvent_t ev = L.count_events[j % (RUN_AHEAD + 1)];
             if (j <= must) SSB_CUDA(cudaEventSynchronize(ev));
             else if (cudaEventQuery(ev) != cudaSuccess) { cudaGetLastError(); break; }
             seen = j;
-            known = (size_t)h_counts[j];
+            known = (size_t)h_ring[slot(j)];
+            hist.push_back((int)known);
         }
         const double t_wait = trace_ms > 0 ? now_ms() : 0.0;
         if (known == 0) break;
         last = it;
-        // While the active set is small (K <= it < gram_iters) q = G[:, active] d costs K rows of G per signal in the
-        // scan kernel -- less than a contraction, a K-atom gather and 16 KB of Q traffic.  Which iterations take that
-        // route depends on the iteration number alone, so a signal's arithmetic does not depend on its batch.
         const bool gram = it < gram_iters;
         a.skip_rhs = (it + 1 < gram_iters) ? 1 : 0;
-        if (!gram) contract(L, tc, cur, known, async ? d_counts + (it - 1) : nullptr);
+        if (!gram) contract(L, tc, cur, known, async ? d_counts + slot(it - 1) : nullptr, false, L.ws_nb);
         a.split = tc ? tc_split : 0;
         a.act = (it == 1) ? nullptr : L.act[cur].template as<int>();
         a.act_next = L.act[cur ^ 1].template as<int>();
-        a.count_in = d_counts + (it - 1);
-        a.next_count = d_counts + it;
+        a.count_in = d_counts + slot(it - 1);
+        a.next_count = d_counts + slot(it);
+        a.count_zero = d_counts + slot(it + 1);
         set_rhs(cur ^ 1, a.split);
         a.it = it;
         const int kb = (int)std::min<uint32_t>(it, (uint32_t)L.ws_kmax);     // K <= kb before iteration `it`
@@ -367,7 +417,6 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const bool gs = !big && (size_t)(kb + 1) * ks * sizeof(T) <= g_budget;
         const size_t smem = homotopy_step_smem<T>(L.ws_kmax, Npad, gs ? kb + 1 : 0, ks);
         SSB_REQUIRE(smem <= 200 * 1024, "max_iterations too large for the step kernel's shared memory");
-        SSB_REQUIRE(L.ws_kmax <= STEP_KR_BIG * 256, "max_iterations too large: the active set is limited to 4096 atoms");
         const size_t slice = homotopy_algebra_slice<T>(kb, ks);
         const int aw = (gram || a.skip_rhs) ? 4 : (split_ok && known >= 1024) ? algebra_warps(slice) : 0;   // few signals: one CTA per signal has the shorter critical path
         const int span = L.begin(timing, 1);
@@ -379,13 +428,13 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
             launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
             L.end(sp_alg);
             L.counters[0] += 2;
-            route[it] = gram ? 3 : 2;
+            route.push_back(gram ? 3 : 2);
         } else {
             const int sp_step = L.begin(timing, 5);
             launch_step(threads, nch, gs, (unsigned)known, smem, st, a, kb, ks);
             L.end(sp_step);
             L.counters[0]++;
-            route[it] = 5;
+            route.push_back(5);
         }
         L.end(span);
         if (sync_iters) {   // debugging aid: find the iteration a device fault belongs to
@@ -395,13 +444,13 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
             const cudaError_t e = cudaStreamSynchronize(st);
             if (e == cudaSuccess) { cudaMemcpy(&hk, a.Kcur, sizeof(int), cudaMemcpyDeviceToHost); cudaMemcpy(&hl, a.lam, sizeof(T), cudaMemcpyDeviceToHost);
                                     cudaMemcpy(&hp, a.gam + (hk > 0 ? hk - 1 : 0), sizeof(uint32_t), cudaMemcpyDeviceToHost); }
-            if (e != cudaSuccess || sync_iters > 1) fprintf(stderr, "[ssb200] it %u known %zu kb %d K[0] %d lam[0] %.9g lastslot %u big %d gs %d aw %d: %s\n", it, known, kb, hk, (double)hl, hp, (int)big, (int)gs, aw, cudaGetErrorString(e));
+            if (e != cudaSuccess || sync_iters > 1) fprintf(stderr, "[ssb200] it %u known %zu kb %d K[0] %d lam[0] %.9g lastslot %u big %d gs %d aw %d exact %d: %s\n", it, known, kb, hk, (double)hl, hp, (int)big, (int)gs, aw, (int)exact, cudaGetErrorString(e));
             SSB_CUDA(e);
         }
         L.counters[3]++;
         SSB_CUDA(cudaEventRecord(L.iter_events[it % (RUN_AHEAD + 1)], st));
         SSB_CUDA(cudaStreamWaitEvent(L.side, L.iter_events[it % (RUN_AHEAD + 1)], 0));
-        SSB_CUDA(cudaMemcpyAsync(h_counts + it, d_counts + it, sizeof(int), cudaMemcpyDeviceToHost, L.side));
+        SSB_CUDA(cudaMemcpyAsync(h_ring + slot(it), d_counts + slot(it), sizeof(int), cudaMemcpyDeviceToHost, L.side));
         SSB_CUDA(cudaEventRecord(L.count_events[it % (RUN_AHEAD + 1)], L.side));
         cur ^= 1;
         if (trace_ms > 0) trace.push_back({ t_begin, t_wait, now_ms(), seen, known });
@@ -409,20 +458,21 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     const double t_loop = trace_ms > 0 ? now_ms() : 0.0;
     SSB_CUDA(cudaStreamSynchronize(st));
     SSB_CUDA(cudaStreamSynchronize(L.side));
+    for (uint32_t j = seen + 1; j <= last; ++j) hist.push_back(h_ring[slot(j)]);   // at most RUN_AHEAD + 1 unread slots, none reused yet
     if (trace_ms > 0 && now_ms() > trace_ms) {
         fprintf(stderr, "[ssb200] slow chunk: %.2f ms (loop queued by %.2f ms, %zu rows)\n", now_ms(), t_loop, rows);
         for (size_t i = 0; i < trace.size(); ++i)
             fprintf(stderr, "[ssb200]   it %3zu begin %8.3f waited %7.3f queued +%6.3f seen %u known %zu\n", i + 1, trace[i].t_begin,
                     trace[i].t_wait - trace[i].t_begin, trace[i].t_queued - trace[i].t_wait, trace[i].seen, trace[i].known);
     }
-    for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)h_counts[it - 1];   // signal-rows contracted in the loop
+    for (uint32_t it = std::max<uint32_t>(1, gram_iters); it <= last; ++it) L.counters[2] += (uint64_t)L.ws_nb * (uint64_t)hist[it - 1];   // signal-rows contracted in the loop
     for (uint32_t it = 1; it <= last; ++it) {
-        const uint64_t n = (uint64_t)h_counts[it - 1];           // signals that entered iteration `it`
-        const uint64_t nc = (uint64_t)h_counts[it];              // ... and continue after it
+        const uint64_t n = (uint64_t)hist[it - 1];           // signals that entered iteration `it`
+        const uint64_t nc = (uint64_t)hist[it];              // ... and continue after it
         const uint64_t kb = std::min<uint64_t>(it, (uint64_t)L.ws_kmax);
-        // algorithmic HBM bytes of the launch: c read + written, q read when it was streamed; the K x K inverse
-        // read + written (K <= kb = it); the next right-hand side written in its container format
-        const uint64_t cq = (uint64_t)Npad * sizeof(T), inv = 2 * kb * kb * sizeof(T), rhs = (uint64_t)Mp * (tc ? 4 : sizeof(T));
+        // algorithmic HBM bytes of the launch: c read (exact mode: the fresh c') + written, q read when it was
+        // streamed; the K x K inverse read + written (K <= kb = it); the next right-hand side(s) written in container format
+        const uint64_t cq = (uint64_t)Npad * sizeof(T), inv = 2 * kb * kb * sizeof(T), rhs = (uint64_t)L.ws_nb * Mp * (tc ? 4 : sizeof(T));
         L.rows[route[it]] += n;
         L.rows[1] += n;
         if (route[it] == 2) L.bytes[2] += n * 3 * cq;
@@ -491,25 +541,22 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     SSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     SSB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
     if (!coop) return false;
-    const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
+    const int kmax = active_set_capacity(max_iter, N);
     const int ks = (kmax + 1) | 1;
     const int grid = std::min(sms, (Npad + 7) / 8);
     const int cnt = (Npad + grid - 1) / grid;
     const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
     if (smem > 200 * 1024) return false;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        SSB_CUDA(cudaFuncSetAttribute(homotopy_single_kernel<T, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = 200 * 1024;
-    }
+    static std::atomic<uint64_t> configured{ 0 };
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS>, configured);
     Lane& L = lane(0);
     cudaStream_t st = L.stream;
-    // workspace: y (padded) | P | Cg | x | part_t | part_max | part_i | iters | errs
-    const size_t nT = (size_t)2 * Mp + Npad + N + 2 * (size_t)grid + 8;
+    // workspace: y (padded) | P | R | Cg | x | part_t | part_max | part_i | iters | errs
+    const size_t nT = (size_t)3 * Mp + Npad + N + 2 * (size_t)grid + 8;
     single_ws_.reserve(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64);
     single_rep_.reserve(64);
     T* w = single_ws_.template as<T>();
-    T* d_y = w; T* d_P = d_y + Mp; T* d_Cg = d_P + Mp; T* d_x = d_Cg + Npad; T* d_pt = d_x + N; T* d_pm = d_pt + grid;
+    T* d_y = w; T* d_P = d_y + Mp; T* d_R = d_P + Mp; T* d_Cg = d_R + Mp; T* d_x = d_Cg + Npad; T* d_pt = d_x + N; T* d_pm = d_pt + grid;
     double* d_err = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(w) + round_up((size_t)(d_pm + grid - w) * sizeof(T), 16));
     uint32_t* d_it = reinterpret_cast<uint32_t*>(d_err + 1);
     uint32_t* d_pi = d_it + 2;
@@ -518,7 +565,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     SingleArgs<T> a{};
     a.N = N; a.Npad = Npad; a.Mp = Mp; a.Kmax = kmax; a.ks = ks;
     a.At = At_; a.G = G_; a.ldg = Npad;
-    a.y = d_y; a.x = x_on_host ? d_x : x; a.P = d_P; a.Cg = d_Cg; a.part_t = d_pt; a.part_i = d_pi; a.part_max = d_pm;
+    a.y = d_y; a.x = x_on_host ? d_x : x; a.P = d_P; a.R = d_R; a.exact = exact_residual() ? 1 : 0; a.Cg = d_Cg; a.part_t = d_pt; a.part_i = d_pi; a.part_max = d_pm;
     a.iters = reports_on_host ? d_it : iters; a.errs = reports_on_host ? d_err : errs;
     a.tol = tol; a.max_iter = max_iter; a.cnt = cnt;
     void* params[] = { &a };
@@ -551,8 +598,9 @@ void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, 
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
     // inputs produced on the caller's stream must be complete before the lanes read them
     SSB_CUDA(cudaStreamSynchronize(user_stream));
+    const int kmax = active_set_capacity(max_iter, N);
+    check_capacity(kmax);                                   // before anything is queued
     if (batch == 1 && solve_single(dY, false, tol, max_iter, dX, false, d_iters, d_errs, false)) return;
-    const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     size_t chunk; int nlanes;
     plan_batch(batch, kmax, false, chunk, nlanes);
     const size_t nchunks = (batch + chunk - 1) / chunk;
@@ -572,8 +620,9 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");
     if (batch == 0) return;
     SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
+    const int kmax = active_set_capacity(max_iter, N);
+    check_capacity(kmax);                                   // before anything is queued
     if (batch == 1 && solve_single(Y, true, tol, max_iter, X, true, iters, errs, true)) return;
-    const int kmax = (int)std::min<uint64_t>((uint64_t)max_iter + 1, (uint64_t)N);
     size_t cap; int nlanes;
     plan_batch(batch, kmax, true, cap, nlanes);
 
@@ -730,7 +779,7 @@ double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int 
         void* lo = split == 2 ? static_cast<void*>(L.Plo[0].template as<__half>() + L.ws_rows * Mp) : split == 1 ? L.Plo[0].p : nullptr;
         const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
         stage_signals_kernel<T><<<blocks, 256, 0, L.stream>>>(dP.as<T>(), (size_t)M, M, (int)rows, hi, lo,
-                                                             L.Pinv[0].template as<float>(), Mp, split);
+                                                             L.Pinv[0].template as<float>(), Mp, split, nullptr);
     }
     SSB_CUDA(cudaGetLastError());
     contract(L, tc, 0, rows, nullptr, true);   // warm-up + the result

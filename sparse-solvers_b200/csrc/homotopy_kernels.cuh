@@ -9,9 +9,14 @@
 //   new direction d_G = inv * sign(c_G, tol)                      homotopy-cpu.cpp:259-266
 //   p = A_G d_G for the next contraction  q = A^T p               homotopy-cpu.cpp:112-120
 //
+// The residual correlation (residual_vector, homotopy-cpu.cpp:87-98, called at :255) comes in two forms:
+//   exact        r = y - A_G x_G is re-formed from the active atoms every iteration, c' = A^T r travels through the same
+//                contraction as q = A^T p (two stacked row blocks), and the step search and lambda = |c'|_inf read that
+//                fresh c'; the direction signs, the stop test and the report use c' - gamma q, ONE step from the fresh base
+//                (never accumulated).  Default wherever the dictionary is coherent (Homotopy::exact_residual).
+//   incremental  c -= gamma*q carried from iteration to iteration (q = A^T A d is already there): one contraction per
+//                iteration.  Inside the reference's own two-BLAS-builds noise floor on incoherent dictionaries only.
 // What differs from the reference by construction (all algebraically identical):
-//   - c is advanced as c -= gamma*q (q = A^T A d is already there) instead of re-forming
-//     A^T (y - A x) from scratch (homotopy-cpu.cpp:87-98);
 //   - A_G^T v for a joining atom v is read from the precomputed Gram matrix G = A^T A instead of
 //     K dot products (online_inverse.h:217-218);
 //   - the active set is kept in slot (insertion) order with a bitmask for membership, not as a
@@ -50,6 +55,7 @@ struct HomArgs {
     int* act_next;    // compacted list for the next iteration
     int* next_count;
     const int* count_in;   // signals entering this iteration, on the device (nullptr: the grid is exact)
+    int* count_zero;       // ring slot of the iteration after next's count: cleared here, its last reader is long done
     uint32_t* mask;   // [Bc][ldc/32] membership bits of the active set (kept by init / algebra / step, read by the scan)
     uint32_t* pick;   // [Bc]        atom chosen by the min-gamma search (split kernels: scan -> algebra)
     T* Pn;            // [rows][ldp] next right-hand sides (full precision, or the TF32 hi part)
@@ -63,6 +69,17 @@ struct HomArgs {
     uint32_t max_iter;
     uint32_t it;      // lockstep iteration number, 1-based
     int dbg;          // timing experiments only (SSB200_DBG): 1 = stop after the c update, 2 = stop before p
+    // ---- exact-residual mode (exact != 0)
+    int exact;
+    const T* Qc;      // [rows][ldc] fresh correlations c' = A^T r, by position (the contraction's second row block)
+    T* C0;            // [Bc][ldc]   A^T y, kept for the Gram iterations (c' = c0 - G_G x_G); nullptr when they are off
+    const T* Y;       // [Bc][ldy]   the signals, caller layout (r = y - A_G x_G)
+    size_t ldy;
+    int M;            // signal length (rows of A); Mp - M padding values of r are zero
+    const float* ymax; // [Bc]       max |y| per signal (bounds r for the fp16 containers)
+    T* Rn;            // [rows][ldp] next residual rows, same container format as Pn
+    T* Rn_lo;
+    float* Rn_inv;
 };
 
 __device__ __forceinline__ float tf32_rna(float x) {
@@ -122,20 +139,24 @@ __device__ __forceinline__ void rhs_rows(const HomArgs<T>& a, int row, void*& hi
 // Y (caller layout) -> first right-hand sides, zero padded to ldp; one warp per signal (split 2 needs the row maximum)
 template <typename T>
 __global__ void stage_signals_kernel(const T* __restrict__ Y, size_t ldy, int M, int rows,
-                                     void* __restrict__ P, void* __restrict__ Plo, float* __restrict__ Pinv, int ldp, int split)
+                                     void* __restrict__ P, void* __restrict__ Plo, float* __restrict__ Pinv, int ldp, int split,
+                                     float* __restrict__ ymax)
 {
     constexpr int V = 16 / sizeof(T);
     const int lane = threadIdx.x & 31;
     const size_t esz = split == 2 ? 2 : sizeof(T);
     for (size_t r = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < (size_t)rows; r += (size_t)gridDim.x * (blockDim.x >> 5)) {
         float scale = 1.f;
-        if (split == 2) {
+        if (split == 2 || ymax) {
             float mx = 0.f;
             for (int m = lane; m < M; m += 32) mx = fmaxf(mx, fabsf((float)Y[r * ldy + m]));
             mx = warp_max(mx);
+            if (ymax && lane == 0) ymax[r] = mx;
+        if (split == 2) {
             const int e = f16_scale_exp(mx);
             scale = ldexpf(1.f, e);
             if (lane == 0) Pinv[r] = ldexpf(1.f, -e);
+        }
         }
         void* hi = static_cast<unsigned char*>(P) + r * ldp * esz;
         void* lo = Plo ? static_cast<unsigned char*>(Plo) + r * ldp * esz : nullptr;
@@ -149,41 +170,86 @@ __global__ void stage_signals_kernel(const T* __restrict__ Y, size_t ldy, int M,
 }
 
 // join-candidate step (lambda -+ c_i) / (1 -+ q_i) (homotopy-cpu.cpp:143-153).  2N of these per signal-iteration make
-// the IEEE division sequence the largest single consumer of issue slots in the step kernel, so float32 uses the
-// hardware reciprocal (<= 2 ulp; c and q already carry more rounding than that, exact cases such as x/1 stay exact).
-__device__ __forceinline__ float step_ratio(float num, float den) { return __fdividef(num, den); }
+// the IEEE division sequence the largest single consumer of issue slots in the step kernel, so float32 ORDERS the candidates
+// with the hardware reciprocal (<= 2 ulp; exact cases such as x/1 stay exact) and the one step that wins is then recomputed
+// with IEEE division (winning_step): the gamma applied to x and c is the reference's quotient.  -DSSB_IEEE_ORDER=1 orders with
+// IEEE division as well (A/B of the parity counts, tests/studies/noise_floor.py).
+#ifndef SSB_IEEE_ORDER
+#define SSB_IEEE_ORDER 0
+#endif
+__device__ __forceinline__ float step_ratio(float num, float den) { return SSB_IEEE_ORDER ? __fdiv_rn(num, den) : __fdividef(num, den); }
 __device__ __forceinline__ double step_ratio(double num, double den) { return num / den; }
+
+// the step of join candidate i in IEEE arithmetic: the smaller strictly positive one of its two ratios (:143-153);
+// `fallback` (the ordering value) when neither qualifies, which only a 2-ulp disagreement at the sign boundary can cause
+template <typename T>
+__device__ __forceinline__ T winning_step(T lam, T c, T q, T fallback) {
+    const T TMAX = num_traits<T>::max();
+    T best = TMAX;
+    const T dl = T(1) - q, dr = T(1) + q;
+    if (dl != T(0)) { const T t = (lam - c) / dl; if (t > T(0) && t < best) best = t; }
+    if (dr != T(0)) { const T t = (lam + c) / dr; if (t > T(0) && t < best) best = t; }
+    return best < TMAX ? best : fallback;
+}
 
 template <typename T>
 __device__ __forceinline__ T sign_tol(T v, T tol) { return v > tol ? T(1) : (v < -tol ? T(-1) : T(0)); }
 
-// p = sum_k d[k] * At[gam[k]][:]  for the CTA's signal, written to row `row` of the next P
+// row `row` of the next residual block (exact mode), as bytes
+template <typename T>
+__device__ __forceinline__ void res_rows(const HomArgs<T>& a, int row, void*& hi, void*& lo) {
+    const size_t esz = a.split == 2 ? 2 : sizeof(T);
+    hi = reinterpret_cast<unsigned char*>(a.Rn) + (size_t)row * a.ldp * esz;
+    lo = a.split ? reinterpret_cast<unsigned char*>(a.Rn_lo) + (size_t)row * a.ldp * esz : nullptr;
+}
+
+// p = sum_k d[k] * At[gam[k]][:]  for the CTA's signal, written to row `row` of the next P; in exact mode also the residual
+// r = y - sum_k x[k] * At[gam[k]][:] (homotopy-cpu.cpp:94-96 over the active atoms: every other x is zero or the
+// rounding residue of a removed atom) to row `row` of the next R, from the same atom rows
 template <typename T, int THREADS>
-__device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, const uint32_t* s_gam, const T* s_d, int K)
+__device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, int sig, const uint32_t* s_gam, const T* s_d, const T* s_x, int K)
 {
     constexpr int V = 16 / sizeof(T);
-    void *pn, *pl;
+    void *pn, *pl, *rn = nullptr, *rl = nullptr;
     rhs_rows(a, row, pn, pl);
-    float scale = 1.f;
-    if (a.split == 2) {   // |p_m| <= amax * sum |d_k|
-        float sd = 0.f;
-        for (int k = 0; k < K; ++k) sd += fabsf((float)s_d[k]);
+    const bool res = a.exact != 0;
+    if (res) res_rows(a, row, rn, rl);
+    float scale = 1.f, rscale = 1.f;
+    if (a.split == 2) {   // |p_m| <= amax * sum |d_k| ; |r_m| <= max |y| + amax * sum |x_k|
+        float sd = 0.f, sx = 0.f;
+        for (int k = 0; k < K; ++k) { sd += fabsf((float)s_d[k]); if (res) sx += fabsf((float)s_x[k]); }
         const int e = f16_scale_exp(sd * a.amax);
         scale = ldexpf(1.f, e);
         if (threadIdx.x == 0) a.Pn_inv[row] = ldexpf(1.f, -e);
+        if (res) {
+            const int er = f16_scale_exp(a.ymax[sig] + sx * a.amax);
+            rscale = ldexpf(1.f, er);
+            if (threadIdx.x == 0) a.Rn_inv[row] = ldexpf(1.f, -er);
+        }
     }
+    const T* y = res ? a.Y + (size_t)sig * a.ldy : nullptr;
     for (int m0 = threadIdx.x * V; m0 < a.Mp; m0 += THREADS * V) {
-        T acc[V];
+        T acc[V], accr[V];
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[e] = T(0);
+        for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
         for (int k = 0; k < K; ++k) {
             T av[V];
             *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
             const T dk = s_d[k];
 #pragma unroll
             for (int e = 0; e < V; ++e) acc[e] += av[e] * dk;
+            if (res) {
+                const T xk = s_x[k];
+#pragma unroll
+                for (int e = 0; e < V; ++e) accr[e] += av[e] * xk;
+            }
         }
         store_rhs<T, V>(a.split, pn, pl, m0, acc, scale);
+        if (res) {
+#pragma unroll
+            for (int e = 0; e < V; ++e) accr[e] = (m0 + e < a.M ? y[m0 + e] : T(0)) - accr[e];
+            store_rhs<T, V>(a.split, rn, rl, m0, accr, rscale);
+        }
     }
 }
 
@@ -198,7 +264,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
     __shared__ T red_v[NW];
     __shared__ uint32_t red_i[NW];
     __shared__ uint32_t s_gam[1];
-    __shared__ T s_d[1];
+    __shared__ T s_d[1], s_x[1];
 
     const int s = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -212,6 +278,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
         T qv[V];
         *reinterpret_cast<int4*>(qv) = *reinterpret_cast<const int4*>(q + i0);
         *reinterpret_cast<int4*>(c + i0) = *reinterpret_cast<const int4*>(qv);
+        if (a.C0) *reinterpret_cast<int4*>(a.C0 + (size_t)s * a.ldc + i0) = *reinterpret_cast<const int4*>(qv);
 #pragma unroll
         for (int e = 0; e < V; ++e) {
             const int i = i0 + e;
@@ -241,6 +308,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
             a.Kcur[s] = 1;
             s_gam[0] = bidx;
             s_d[0] = d0;
+            s_x[0] = T(0);
         }
     }
     __syncthreads();
@@ -248,7 +316,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_init_kernel(HomArgs<T> a)
         const uint32_t g = s_gam[0];
         for (int w = tid; w < (a.ldc >> 5); w += THREADS) a.mask[(size_t)s * (a.ldc >> 5) + w] = (w == (int)(g >> 5)) ? 1u << (g & 31) : 0u;
     }
-    write_rhs<T, THREADS>(a, s, s_gam, s_d, 1);
+    write_rhs<T, THREADS>(a, s, s, s_gam, s_d, s_x, 1);   // exact mode: r = y - 0
 }
 
 // out[r] = sum_k G[r][k] v[k] for the K x K inverse (the reference's K x K xgemv, homotopy-cpu.cpp:263 and
@@ -295,7 +363,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     __shared__ uint32_t red_i[NW];
     __shared__ T sh_gamma, sh_lam;
     __shared__ uint32_t sh_idx;
-    __shared__ int sh_slot, sh_row;
+    __shared__ int sh_slot, sh_row, sh_join;
 
     const int KC = (a.Kmax + 2) & ~1;   // even, keeps the arrays behind it 8-byte aligned
     T* s_d = reinterpret_cast<T*>(smem_raw);
@@ -309,6 +377,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     T* s_G = reinterpret_cast<T*>(mask + ((mask_words + 3) & ~3));
 
     const int pos = blockIdx.x;
+    if (a.count_zero && pos == 0 && threadIdx.x == 0) *a.count_zero = 0;   // before the early exit: an empty iteration clears it too
     if (a.count_in && pos >= *a.count_in) return;   // grid sized from a stale (larger) count
     const int s = a.act ? a.act[pos] : pos;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -318,6 +387,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     T* Ginv = a.Ginv + (size_t)s * a.Kmax * a.Kmax;
     T* c = a.C + (size_t)s * a.ldc;
     const T* q = a.Q + (size_t)pos * a.ldc;
+    // exact mode: the search reads the fresh c' = A^T r of this iteration (second row block of the contraction)
+    const T* csrc = a.exact ? a.Qc + (size_t)pos * a.ldc : c;
     T* x = a.X + (size_t)s * a.ldx;
     const T TMAX = num_traits<T>::max();
     T* Gm = GS ? s_G : Ginv;              // where the inverse is worked on
@@ -330,7 +401,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         for (int ch = 0; ch < NCH; ++ch) {
             const int i0 = (ch * THREADS + tid) * V;
             if (i0 < a.ldc) {
-                *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(c + i0);
+                *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(csrc + i0);
                 *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
             }
         }
@@ -351,8 +422,23 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         }
     }
     const int K = a.Kcur[s];
-    const T lam = a.lam[s];
+    T lam = a.lam[s];
     for (int k = tid; k < kb; k += THREADS) { s_gam[k] = gam[k]; s_d[k] = dG[k]; }   // K <= kb = min(it, Kmax)
+    if (a.exact) {   // lambda = |c'|_inf over the same vector the search reads (:270 on the re-formed c, :255)
+        T mx0 = T(0);
+        if constexpr (NCH > 0) {
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                const int i0 = (ch * THREADS + tid) * V;
+#pragma unroll
+                for (int e = 0; e < V; ++e) if (i0 + e < a.N) mx0 = max(mx0, fabs(cv[ch][e]));
+            }
+        } else {
+            for (int i = tid; i < a.N; i += THREADS) mx0 = max(mx0, fabs(csrc[i]));
+        }
+        mx0 = warp_max(mx0);
+        if (lane == 0) red_v[warp] = mx0;   // read after the next barrier, rewritten only after the one that follows it
+    }
     if constexpr (GS) {
         // flat copy, 8 independent loads in flight per thread (row = e / kb by multiply-high: exact for e*kb < 2^32)
         const uint32_t total = (uint32_t)(kb * kb), magic = (uint32_t)((0x100000000ull + kb - 1) / kb);
@@ -374,6 +460,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     }
     for (int w = tid; w < mask_words; w += THREADS) mask[w] = 0u;
     __syncthreads();
+    if (a.exact) {
+        lam = red_v[0];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) lam = max(lam, red_v[w]);
+    }
     // per-slot values stay in registers (slot k lives in thread k % THREADS) so that no load is waited for
     // before its value is needed: x at the active atoms, the Gram row of a joining atom, c at the active atoms
     T xk[KR], u1r[KR], cgr[KR];   // K <= KR * THREADS (checked by the host)
@@ -434,7 +525,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     } else {
         for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
             T cc[V], qq[V];
-            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(csrc + i0);
             *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
             scan(cc, qq, i0);
         }
@@ -457,6 +548,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         bidx = lane < NW ? red_i[lane] : 0xffffffffu;
         warp_argmin(best, bidx);
         if (lane == 0) {
+            sh_join = bidx != 0xffffffffu;
             if (bidx == 0xffffffffu) bidx = 0;   // no candidate: (max, 0) -- the caller toggles column 0 (:122-123)
             sh_gamma = best;
             sh_idx = bidx;
@@ -464,9 +556,24 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         }
     }
     __syncthreads();
-    const T gamma = sh_gamma;
     const uint32_t idx = sh_idx;
     const bool present = (mask[idx >> 5] >> (idx & 31)) & 1u;
+    if constexpr (sizeof(T) == 4) {
+        // the winning join step again, in IEEE arithmetic (the ordering used the hardware reciprocal)
+        if (sh_join && !present && !SSB_IEEE_ORDER) {
+            if constexpr (NCH > 0) {
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch) {
+                    const int i0 = (ch * THREADS + tid) * V;
+#pragma unroll
+                    for (int e = 0; e < V; ++e)
+                        if ((uint32_t)(i0 + e) == idx) sh_gamma = winning_step(lam, cv[ch][e], qv[ch][e], sh_gamma);
+                }
+            } else if (tid == 0) sh_gamma = winning_step(lam, csrc[idx], q[idx], sh_gamma);
+            __syncthreads();   // sh_join and present are block-uniform
+        }
+    }
+    const T gamma = sh_gamma;
     if (present)
         for (int k = tid; k < K; k += THREADS) if (s_gam[k] == idx) sh_slot = k;
     const int Knew = present ? K - 1 : K + 1;
@@ -485,16 +592,18 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             if (k < K) u1r[u] = a.G[(size_t)idx * a.ldg + s_gam[k]];
         }
         dot = a.G[(size_t)idx * a.ldg + idx];                                                 // v.v
+        if (a.exact && tid == 0) s_x[K] = x[idx];   // 0, or the rounding residue of an atom that left earlier
     }
 
     // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
-        if (k < K) x[s_gam[k]] = xk[u] + gamma * s_d[k];
+        if (k < K) { const T xn = xk[u] + gamma * s_d[k]; x[s_gam[k]] = xn; if (a.exact) s_x[k] = xn; }
     }
 
-    // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
+    // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270).  Exact mode: c is this iteration's fresh
+    // c' = A^T r, so the result is one step from a re-formed base; incremental mode: c carries over from iteration to iteration
     T mx = T(0);
     auto update = [&](T (&cc)[V], const T (&qq)[V], int i0) {
 #pragma unroll
@@ -513,7 +622,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
     } else {
         for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
             T cc[V], qq[V];
-            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(csrc + i0);
             *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
             update(cc, qq, i0);
         }
@@ -590,7 +699,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
                 Gm[(size_t)j * ldm + k] = vrow;
                 Gm[(size_t)k * ldm + j] = vcol;
             }
-            if (tid == 0) { const uint32_t g = s_gam[last]; s_gam[j] = g; gam[j] = g; s_cg[j] = s_cg[last]; }
+            if (tid == 0) { const uint32_t g = s_gam[last]; s_gam[j] = g; gam[j] = g; s_cg[j] = s_cg[last]; if (a.exact) s_x[j] = s_x[last]; }
         }
     }
     __syncthreads();
@@ -622,7 +731,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         }
     }
     __syncthreads();
-    if (cont && a.dbg != 2) write_rhs<T, THREADS>(a, sh_row, s_gam, s_d, Knew);
+    if (cont && a.dbg != 2) write_rhs<T, THREADS>(a, sh_row, s, s_gam, s_d, s_x, Knew);
 }
 
 // dynamic shared memory of the step kernel: per-slot vectors, membership mask, and (when held on chip) the inverse

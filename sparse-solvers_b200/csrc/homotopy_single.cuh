@@ -8,6 +8,9 @@
 //   phase 3  CTA 0      x += gamma d, toggle, online inverse update (in shared memory for the whole solve), new d,
 //                       p = A_G d (:166-183, :259-266, online_inverse.h:183-293); all CTAs: stop test (:272)
 // Same formulas, summation orders and quirks as homotopy_step_kernel; the dictionary (1-4 MB) streams from L2.
+// Exact-residual mode (SingleArgs::exact, see homotopy_kernels.cuh): CTA 0 also re-forms r = y - A_G x_G in phase 3, phase 1
+// takes c' = A^T r and q = A^T p from ONE pass over the CTA's atoms, and a fourth grid barrier publishes lambda = |c'|_inf
+// before the search.  All divisions here are IEEE (a CTA looks at ~N/148 candidates per iteration).
 #pragma once
 
 #include <cooperative_groups.h>
@@ -23,6 +26,8 @@ struct SingleArgs {
     const T* y;           // [Mp] zero padded signal
     T* x;                 // [N] output (zeroed by the kernel)
     T* P;                 // [Mp] scratch: current right-hand side
+    T* R;                 // [Mp] scratch: current residual (exact mode)
+    int exact;
     T* Cg;                // [Npad] scratch: c, published every iteration
     T* part_t; uint32_t* part_i; T* part_max;   // [grid] partials
     uint32_t* iters; double* errs;
@@ -33,7 +38,7 @@ struct SingleArgs {
 template <typename T>
 inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks) {
     const size_t KC = (size_t)((Kmax + 2) & ~1);
-    return ((size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64;
+    return (2 * (size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64;
 }
 
 template <typename T, int THREADS>
@@ -51,7 +56,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
 
     const int KC = (a.Kmax + 2) & ~1;
     T* s_p = reinterpret_cast<T*>(smem_raw);          // [Mp]
-    T* s_c = s_p + a.Mp;                              // [cnt]
+    T* s_r = s_p + a.Mp;                              // [Mp]   residual (exact mode)
+    T* s_c = s_r + a.Mp;                              // [cnt]
     T* s_q = s_c + a.cnt;                             // [cnt]
     T* s_G = s_q + a.cnt;                             // [(Kmax+1) * ks]   CTA 0 only from here on
     T* s_d = s_G + (size_t)(a.Kmax + 1) * a.ks;
@@ -80,6 +86,22 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             }
             acc = warp_sum(acc);
             if (lane == 0) s_q[n - a0] = acc;
+        }
+    };
+    // exact mode: c' = A^T r and q = A^T p over the slice from one pass over its atoms
+    auto correlate2 = [&]() {
+        for (int n = a0 + warp; n < a1; n += NW) {
+            const T* row = a.At + (size_t)n * a.Mp;
+            T accq = T(0), accc = T(0);
+            for (int m = lane * V; m < a.Mp; m += 32 * V) {
+                T av[V];
+                *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(row + m));
+#pragma unroll
+                for (int v = 0; v < V; ++v) { accq += av[v] * s_p[m + v]; accc += av[v] * s_r[m + v]; }
+            }
+            accq = warp_sum(accq);
+            accc = warp_sum(accc);
+            if (lane == 0) { s_q[n - a0] = accq; s_c[n - a0] = accc; }
         }
     };
     // block-wide lexicographic min of (value, index); bit 31 of the index may carry the leave flag
@@ -141,7 +163,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             }
             __syncthreads();
             const T d0 = s_d[0];
-            for (int m = tid; m < a.Mp; m += THREADS) a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
+            for (int m = tid; m < a.Mp; m += THREADS) {
+                a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
+                if (a.exact) a.R[m] = a.y[m];                      // r = y - A 0
+            }
         }
     }
     __threadfence();
@@ -151,10 +176,29 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     uint32_t it = 0;
     for (;;) {
         ++it;
-        for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = __ldcg(a.P + m);
+        for (int m = tid; m < a.Mp; m += THREADS) { s_p[m] = __ldcg(a.P + m); if (a.exact) s_r[m] = __ldcg(a.R + m); }
         __syncthreads();
-        correlate(s_p);
+        if (a.exact) correlate2(); else correlate(s_p);
         __syncthreads();
+        if (a.exact) {   // lambda = |c'|_inf over the re-formed correlations (:270 on :255's c)
+            T mx0 = T(0);
+            for (int n = a0 + tid; n < a1 && n < a.N; n += THREADS) mx0 = max(mx0, fabs(s_c[n - a0]));
+            mx0 = warp_max(mx0);
+            if (lane == 0) red_v[warp] = mx0;
+            __syncthreads();
+            if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); a.part_max[cta] = m; }
+            __threadfence();
+            grid.sync();
+            T l2 = T(0);
+            for (int g = tid; g < G; g += THREADS) l2 = max(l2, __ldcg(a.part_max + g));
+            l2 = warp_max(l2);
+            __syncthreads();
+            if (lane == 0) red_v[warp] = l2;
+            __syncthreads();
+            lam = red_v[0];
+            for (int w = 1; w < NW; ++w) lam = max(lam, red_v[w]);
+            __syncthreads();
+        }
         // min-gamma search (:122-163): join candidates of the slice, leave candidates in CTA 0
         T best = TMAX;
         uint32_t bidx = 0xffffffffu;
@@ -162,8 +206,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             if (s_act[n - a0]) continue;
             const T cc = s_c[n - a0], qq = s_q[n - a0];
             const T dl = T(1) - qq, dr = T(1) + qq;
-            if (dl != T(0)) { const T t = step_ratio(lam - cc, dl); if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
-            if (dr != T(0)) { const T t = step_ratio(lam + cc, dr); if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
+            if (dl != T(0)) { const T t = (lam - cc) / dl; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
+            if (dr != T(0)) { const T t = (lam + cc) / dr; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
         }
         if (cta == 0)
             for (int k = tid; k < K; k += THREADS) {
@@ -280,19 +324,24 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             __syncthreads();
             matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
             __syncthreads();
-            if (cont) {   // p = A_G d (:112-116), k ascending per element as write_rhs
+            if (cont) {   // p = A_G d (:112-116), k ascending per element as write_rhs; exact mode: r = y - A_G x_G (:94-96)
                 for (int m0 = tid * V; m0 < a.Mp; m0 += THREADS * V) {
-                    T acc[V];
+                    T acc[V], accr[V];
 #pragma unroll
-                    for (int e = 0; e < V; ++e) acc[e] = T(0);
+                    for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
                     for (int k = 0; k < Knew; ++k) {
                         T av[V];
                         *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
-                        const T dk = s_d[k];
+                        const T dk = s_d[k], xk = s_x[k];
 #pragma unroll
-                        for (int e = 0; e < V; ++e) acc[e] += av[e] * dk;
+                        for (int e = 0; e < V; ++e) { acc[e] += av[e] * dk; accr[e] += av[e] * xk; }
                     }
                     *reinterpret_cast<int4*>(a.P + m0) = *reinterpret_cast<const int4*>(acc);
+                    if (a.exact) {
+#pragma unroll
+                        for (int e = 0; e < V; ++e) accr[e] = a.y[m0 + e] - accr[e];    // y is zero padded to Mp
+                        *reinterpret_cast<int4*>(a.R + m0) = *reinterpret_cast<const int4*>(accr);
+                    }
                 }
             } else if (tid == 0) { *a.iters = it; *a.errs = (double)lam_new; }   // :274
         }

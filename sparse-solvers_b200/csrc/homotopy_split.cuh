@@ -42,20 +42,25 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
 {
     constexpr int GRAM_KMAX = 32;
     __shared__ uint32_t s_gq[GRAMQ ? GRAM_KMAX : 1];
-    __shared__ T s_dq[GRAMQ ? GRAM_KMAX : 1];
+    __shared__ T s_dq[GRAMQ ? GRAM_KMAX : 1], s_xq[GRAMQ ? GRAM_KMAX : 1];
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;
-    __shared__ T red_v[NW];
+    __shared__ T red_v[NW], red_m[NW];
     __shared__ uint32_t red_i[NW];
     __shared__ T sh_gamma;
     __shared__ uint32_t sh_idx;
+    __shared__ int sh_join;
 
     const int pos = blockIdx.x;
+    if (a.count_zero && pos == 0 && threadIdx.x == 0) *a.count_zero = 0;   // before the early exit: an empty iteration clears it too
     if (a.count_in && pos >= *a.count_in) return;   // grid sized from a stale (larger) count
     const int s = a.act ? a.act[pos] : pos;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     T* c = a.C + (size_t)s * a.ldc;
     const T* q = a.Q + (size_t)pos * a.ldc;
+    // exact mode: the search reads this iteration's fresh c' -- the contraction's second row block, or, on a Gram iteration,
+    // c0 - G_G x_G formed below from the same rows of G that give q
+    const T* csrc = a.exact ? (GRAMQ ? a.C0 + (size_t)s * a.ldc : a.Qc + (size_t)pos * a.ldc) : c;
     T* x = a.X + (size_t)s * a.ldx;
     const uint32_t* maskg = a.mask + (size_t)s * (a.ldc >> 5);
     const T TMAX = num_traits<T>::max();
@@ -69,14 +74,14 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             if (i0 < a.ldc) {
                 // (evict-first loads were measured and lose 8 %: a third of q is still in L2 from the contraction)
                 // (walking the positions last to first, to meet the rows the contraction wrote last: no change)
-                *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(c + i0);
+                *reinterpret_cast<int4*>(cv[ch]) = *reinterpret_cast<const int4*>(csrc + i0);
                 if constexpr (!GRAMQ) *reinterpret_cast<int4*>(qv[ch]) = *reinterpret_cast<const int4*>(q + i0);
                 mwr[ch] = maskg[i0 >> 5];
             }
         }
     }
     const int K = a.Kcur[s];
-    const T lam = a.lam[s];
+    T lam = a.lam[s];
     constexpr int KR = 3;   // K <= KR * THREADS (checked by the host)
     uint32_t gk[KR];
     T dk[KR], xk[KR];
@@ -91,8 +96,9 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         if (k < K) xk[u] = x[gk[u]];
     }
     if constexpr (GRAMQ && NCH > 0) {
-        if (tid < kb) { s_gq[tid] = gk[0]; s_dq[tid] = dk[0]; }   // kb <= GRAM_KMAX <= THREADS (checked by the host)
+        if (tid < kb) { s_gq[tid] = gk[0]; s_dq[tid] = dk[0]; if (tid < K) s_xq[tid] = xk[0]; }   // kb <= GRAM_KMAX <= THREADS (checked by the host)
         __syncthreads();
+        const bool ex = a.exact != 0;
 #pragma unroll
         for (int ch = 0; ch < NCH; ++ch) {
             const int i0 = (ch * THREADS + tid) * V;
@@ -107,8 +113,32 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
                     const T d = s_dq[k];
 #pragma unroll
                     for (int e = 0; e < V; ++e) qv[ch][e] += gv[e] * d;
+                    if (ex) {   // c' = A^T y - G_G x_G, re-formed every iteration
+                        const T xg = s_xq[k];
+#pragma unroll
+                        for (int e = 0; e < V; ++e) cv[ch][e] -= gv[e] * xg;
+                    }
                 }
         }
+    }
+    if (a.exact) {   // lambda = |c'|_inf over the vector the search reads (:270 on the re-formed c)
+        T mx0 = T(0);
+        if constexpr (NCH > 0) {
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                const int i0 = (ch * THREADS + tid) * V;
+#pragma unroll
+                for (int e = 0; e < V; ++e) if (i0 + e < a.N) mx0 = max(mx0, fabs(cv[ch][e]));
+            }
+        } else {
+            for (int i = tid; i < a.N; i += THREADS) mx0 = max(mx0, fabs(csrc[i]));
+        }
+        mx0 = warp_max(mx0);
+        if (lane == 0) red_m[warp] = mx0;
+        __syncthreads();
+        lam = red_m[0];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) lam = max(lam, red_m[w]);
     }
 
     // ---- min-gamma search (find_max_gamma part 2, :122-163): smallest strictly positive step, ties -> lowest index.
@@ -155,7 +185,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     } else {
         for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
             T cc[V], qq[V];
-            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(csrc + i0);
             *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
             scan(cc, qq, i0, maskg[i0 >> 5]);
         }
@@ -178,15 +208,31 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         warp_argmin_flagged(best, bidx);
         if (lane == 0) {
             // no candidate: (max, 0) -- the caller toggles column 0 (:122-123), whichever side it is on
+            sh_join = bidx != 0xffffffffu && !(bidx >> 31);
             if (bidx == 0xffffffffu) bidx = (maskg[0] & 1u) ? 0x80000000u : 0u;
             sh_gamma = best;
             sh_idx = bidx;
         }
     }
     __syncthreads();
-    const T gamma = sh_gamma;
     const bool present = (sh_idx >> 31) != 0;
     const uint32_t idx = sh_idx & 0x7fffffffu;
+    if constexpr (sizeof(T) == 4) {
+        // the winning join step again, in IEEE arithmetic (the ordering used the hardware reciprocal)
+        if (sh_join && !SSB_IEEE_ORDER) {
+            if constexpr (NCH > 0) {
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch) {
+                    const int i0 = (ch * THREADS + tid) * V;
+#pragma unroll
+                    for (int e = 0; e < V; ++e)
+                        if ((uint32_t)(i0 + e) == idx) sh_gamma = winning_step(lam, cv[ch][e], qv[ch][e], sh_gamma);
+                }
+            } else if (tid == 0) sh_gamma = winning_step(lam, csrc[idx], q[idx], sh_gamma);
+            __syncthreads();   // sh_join is block-uniform
+        }
+    }
+    const T gamma = sh_gamma;
     const int Knew = present ? K - 1 : K + 1;
     if (Knew == 0) {   // :248-249: the last atom left; x, c and lambda stay as they were
         if (tid == 0) { a.iters[s] = a.it; a.errs[s] = (double)lam; a.Kcur[s] = 0; }
@@ -200,7 +246,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         if (k < K) x[gk[u]] = xk[u] + gamma * dk[u];
     }
 
-    // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270)
+    // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270); exact mode: one step from the fresh c'
     T mx = T(0);
     auto update = [&](T (&cc)[V], const T (&qq)[V], int i0) {
 #pragma unroll
@@ -219,7 +265,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     } else {
         for (int i0 = tid * V; i0 < a.N; i0 += THREADS * V) {
             T cc[V], qq[V];
-            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(c + i0);
+            *reinterpret_cast<int4*>(cc) = *reinterpret_cast<const int4*>(csrc + i0);
             *reinterpret_cast<int4*>(qq) = *reinterpret_cast<const int4*>(q + i0);
             update(cc, qq, i0);
         }
@@ -387,26 +433,42 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
     }
     __syncwarp();
 
-    // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs
-    if (a.skip_rhs) return;   // the next iteration forms q from the Gram matrix: no right-hand side needed
-    void *pn, *pl;
+    // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs; in exact mode also the
+    // residual r = y - A_G x_G (:94-96 over the active atoms) from the same atom rows
+    if (a.skip_rhs) return;   // the next iteration forms q (and c') from the Gram matrix: no right-hand side needed
+    const bool res = a.exact != 0;
+    T* s_x = s_u2;            // free since the inverse update
+    if (res) {
+        const T* x = a.X + (size_t)s * a.ldx;
+        for (int k = lane; k < Knew; k += 32) s_x[k] = x[s_gam[k]];
+        __syncwarp();
+    }
+    void *pn, *pl, *rn = nullptr, *rl = nullptr;
     rhs_rows(a, row, pn, pl);
-    float scale = 1.f;
-    if (a.split == 2) {   // |p_m| <= amax * sum |d_k|
-        float sd = 0.f;
-        for (int k = lane; k < Knew; k += 32) sd += fabsf((float)s_d[k]);
+    if (res) res_rows(a, row, rn, rl);
+    float scale = 1.f, rscale = 1.f;
+    if (a.split == 2) {   // |p_m| <= amax * sum |d_k| ; |r_m| <= max |y| + amax * sum |x_k|
+        float sd = 0.f, sx = 0.f;
+        for (int k = lane; k < Knew; k += 32) { sd += fabsf((float)s_d[k]); if (res) sx += fabsf((float)s_x[k]); }
         sd = warp_sum(sd);
         const int e = f16_scale_exp(sd * a.amax);
         scale = ldexpf(1.f, e);
         if (lane == 0) a.Pn_inv[row] = ldexpf(1.f, -e);
+        if (res) {
+            sx = warp_sum(sx);
+            const int er = f16_scale_exp(a.ymax[s] + sx * a.amax);
+            rscale = ldexpf(1.f, er);
+            if (lane == 0) a.Rn_inv[row] = ldexpf(1.f, -er);
+        }
     }
+    const T* y = res ? a.Y + (size_t)s * a.ldy : nullptr;
     // two 16-byte chunks of p per pass, four atoms per batch: 8 independent loads in flight per lane, and the active
     // set, the direction and the row address are fetched once per atom for both chunks
     for (int mb = lane * V; mb < a.Mp; mb += 2 * 32 * V) {
         const bool two = mb + 32 * V < a.Mp;   // warp-uniform
-        T acc0[V], acc1[V];
+        T acc0[V], acc1[V], rac0[V], rac1[V];
 #pragma unroll
-        for (int e = 0; e < V; ++e) { acc0[e] = T(0); acc1[e] = T(0); }
+        for (int e = 0; e < V; ++e) { acc0[e] = T(0); acc1[e] = T(0); rac0[e] = T(0); rac1[e] = T(0); }
         int k = 0;
         for (; k + 4 <= Knew; k += 4) {
             T a0[4][V], a1[4][V];
@@ -425,6 +487,15 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
 #pragma unroll
                     for (int e = 0; e < V; ++e) acc1[e] += a1[u][e] * dk;
                 }
+                if (res) {
+                    const T xk = s_x[k + u];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) rac0[e] += a0[u][e] * xk;
+                    if (two) {
+#pragma unroll
+                        for (int e = 0; e < V; ++e) rac1[e] += a1[u][e] * xk;
+                    }
+                }
             }
         }
         for (; k < Knew; ++k) {
@@ -439,9 +510,28 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
 #pragma unroll
                 for (int e = 0; e < V; ++e) acc1[e] += a1[e] * dk;
             }
+            if (res) {
+                const T xk = s_x[k];
+#pragma unroll
+                for (int e = 0; e < V; ++e) rac0[e] += a0[e] * xk;
+                if (two) {
+#pragma unroll
+                    for (int e = 0; e < V; ++e) rac1[e] += a1[e] * xk;
+                }
+            }
         }
         store_rhs<T, V>(a.split, pn, pl, mb, acc0, scale);
         if (two) store_rhs<T, V>(a.split, pn, pl, mb + 32 * V, acc1, scale);
+        if (res) {
+#pragma unroll
+            for (int e = 0; e < V; ++e) rac0[e] = (mb + e < a.M ? y[mb + e] : T(0)) - rac0[e];
+            store_rhs<T, V>(a.split, rn, rl, mb, rac0, rscale);
+            if (two) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) rac1[e] = (mb + 32 * V + e < a.M ? y[mb + 32 * V + e] : T(0)) - rac1[e];
+                store_rhs<T, V>(a.split, rn, rl, mb + 32 * V, rac1, rscale);
+            }
+        }
     }
 }
 

@@ -149,7 +149,7 @@ public:
         for (size_t b0 = 0; b0 < batch; b0 += chunk) {
             const size_t rows = std::min(chunk, batch - b0);
             const int blocks = (int)std::min<size_t>(8192, (rows + 7) / 8);
-            stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY + b0 * ldy, ldy, M, (int)rows, P_.as<T>(), nullptr, nullptr, Mp, 0);
+            stage_signals_kernel<T><<<blocks, 256, 0, st>>>(dY + b0 * ldy, ldy, M, (int)rows, P_.as<T>(), nullptr, nullptr, Mp, 0, nullptr);
             SSB_CUDA(cudaGetLastError());
             counters[0]++;
             // S = Q^T Y  (irls-cpu.cpp:53, the same for every iteration of a signal)

@@ -75,6 +75,9 @@ struct SolverBase {
     }
 };
 
+// a multi-GPU group of homotopy handles (group.cuh)
+struct GroupBase { bool is_f64 = false; virtual ~GroupBase() {} };
+
 // contract_tc.cu: Q[r][n] = sum_m At[n][m] P[r][m] on the tcgen05 pipe, 3xTF32 (hi*hi + hi*lo + lo*hi).
 // At_hi/At_lo: [n_pad][mp], P_hi/P_lo: [rows_alloc][mp] with rows_alloc % 256 == 0 (rows beyond
 // `rows` are computed but not stored), Q: [rows][ldq].  n_pad % 128 == 0, mp % 32 == 0.
@@ -84,8 +87,11 @@ struct TcPlan;   // holds the TMA descriptors of one (At, P, Q) buffer set
 TcPlan* tc_plan_create(bool f16, const void* At_hi, const void* At_lo, int n_pad, int mp, const void* P_hi, const void* P_lo,
                        int rows_alloc, const float* a_inv, const float* p_inv);
 void tc_plan_destroy(TcPlan*);
-// rows is an upper bound when rows_dev (device int) is given: the kernel uses min(rows, *rows_dev)
-void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev = nullptr);
+// rows is an upper bound when rows_dev (device int) is given: the kernel uses min(rows, *rows_dev).
+// nblk > 1: the same `rows` rows of nblk row blocks that start blk_off rows apart in P and in Q (blk_off % 256 == 0) --
+// the exact-residual mode contracts the directions' block and the residuals' block in one launch
+void tc_contract(TcPlan* plan, int rows, float* Q, int ldq, cudaStream_t stream, const int* rows_dev = nullptr,
+                 int nblk = 1, int blk_off = 0);
 bool tc_supported(int n_pad, int mp);
 
 }  // namespace ssb

@@ -14,7 +14,7 @@ import numpy as np
 
 from ._lib import SolverError, check, lib
 
-__all__ = ["Homotopy", "Irls", "HomotopyReport", "IrlsReport", "version", "SolverError",
+__all__ = ["Homotopy", "HomotopyGroup", "Irls", "HomotopyReport", "IrlsReport", "version", "SolverError",
            "reconstruct_signal", "norm_l1"]
 
 
@@ -200,11 +200,18 @@ class Homotopy(_Solver):
         tol, mi = self._defaults(tolerance, max_iterations)
         B = Y.shape[0]
         X = out if out is not None else np.empty((B, self.shape[1]), dtype=self.dtype)
+        if out is not None:      # the C side writes B rows of N values through this pointer: everything it assumes is checked here
+            if not isinstance(X, np.ndarray) or X.dtype != self.dtype or X.shape != (B, self.shape[1]):
+                raise ValueError(f"out must be a numpy array of dtype {self.dtype} and shape ({B}, {self.shape[1]})")
+            if X.strides[1] != X.itemsize or (B > 1 and X.strides[0] < self.shape[1] * X.itemsize) or X.strides[0] % X.itemsize:
+                raise ValueError("out must have unit inner stride and non-overlapping rows")
+            if not X.flags.writeable:
+                raise ValueError("out is read-only")
         iters = np.empty(B, dtype=np.uint32)
         errs = np.empty(B, dtype=np.float64)
         fn = getattr(lib(), f"ssb200_homotopy_solve_batch_{self._sfx}")
         check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
-                 _ptr(X), C.c_size_t(X.strides[0] // X.itemsize), _ptr(iters), _ptr(errs)))
+                 _ptr(X), C.c_size_t(X.strides[0] // X.itemsize if B > 1 else self.shape[1]), _ptr(iters), _ptr(errs)))
         return X, iters, errs
 
     def _solve_batch_cuda(self, Y, tolerance, max_iterations, out, sparse):
@@ -246,6 +253,19 @@ class Homotopy(_Solver):
             check(fn(self._h, C.c_void_p(y_ptr), C.c_size_t(batch), C.c_size_t(ldy), tol, mi, C.c_void_p(x_ptr),
                      C.c_size_t(ldx), C.c_void_p(iters_ptr), C.c_void_p(errs_ptr)))
 
+    RESIDUAL_MODES = {"auto": 0, "exact": 1, "incremental": 2}
+
+    def set_residual_mode(self, mode):
+        """How c = A^T (y - A x) is kept (include/ssb200.h): "exact" re-forms it every iteration as the reference does
+        (homotopy-cpu.cpp:87-98, :255), "incremental" carries c -= gamma q, "auto" (default) picks by the dictionary's coherence."""
+        check(lib().ssb200_homotopy_set_residual_mode(self._h, C.c_int(self.RESIDUAL_MODES[mode])))
+
+    def residual_info(self):
+        """(mode in effect: "exact" | "incremental", mutual coherence of the dictionary)"""
+        mode, mu = C.c_int(), C.c_double()
+        check(lib().ssb200_homotopy_get_residual_info(self._h, C.byref(mode), C.byref(mu)))
+        return ("exact" if mode.value == 1 else "incremental"), mu.value
+
     def debug_contract(self, P, path="simt", reps=1):
         """Test/bench hook: Q[r] = A^T P[r] through one contraction kernel; returns (Q, ms per launch)."""
         P = np.ascontiguousarray(P, dtype=self.dtype)
@@ -286,6 +306,75 @@ class Homotopy(_Solver):
         check(getattr(lib(), f"ssb200_reconstruct_batch_{self._sfx}")(
             self._h, _ptr(X), C.c_size_t(X.shape[0]), C.c_size_t(X.shape[1]), _ptr(Y), C.c_size_t(Y.shape[1])))
         return Y
+
+
+class HomotopyGroup:
+    """One process, several GPUs of the box (ssb200_group_*, include/ssb200.h): the dictionary is replicated with one NCCL
+    broadcast, solve_batch cuts the batch into contiguous shards, one host thread per GPU; results come back in the caller's
+    arrays.  New functionality (the reference solves one signal per call on the CPU, include/ss/ss.h:50)."""
+
+    def __init__(self, A, devices=None):
+        A = np.asarray(A)
+        if A.ndim != 2:
+            raise ValueError("A must be 2-dimensional")
+        if A.dtype not in _SFX:
+            raise TypeError("A must be float32 or float64")
+        if devices is None:
+            devices = list(range(max(1, lib().ssb200_device_count())))
+        self.devices = [int(d) for d in devices]
+        self._sfx, self._ct = _SFX[A.dtype]
+        self.dtype, self.shape = A.dtype, A.shape
+        self._g = C.c_void_p()
+        devs = (C.c_int * len(self.devices))(*self.devices)
+        rs, cs = A.strides[0] // A.itemsize, A.strides[1] // A.itemsize
+        check(getattr(lib(), f"ssb200_group_create_{self._sfx}")(_ptr(A), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]), C.c_ssize_t(rs),
+                                                                 C.c_ssize_t(cs), devs, C.c_int(len(self.devices)), C.byref(self._g)))
+
+    def __del__(self):
+        g = getattr(self, "_g", None)
+        if g is not None and g.value:
+            lib().ssb200_group_destroy(g)
+            self._g = C.c_void_p()
+
+    def __len__(self):
+        return int(lib().ssb200_group_size(self._g))
+
+    def set_residual_mode(self, mode):
+        check(lib().ssb200_group_set_residual_mode(self._g, C.c_int(Homotopy.RESIDUAL_MODES[mode])))
+
+    def solve_batch(self, Y, tolerance=None, max_iterations=100):
+        """Y: (B, M) host array or a CUDA tensor on the group's first device.  Returns X, iters, solution_errors of the same kind."""
+        tol = self._ct(10 * np.finfo(self.dtype).eps if tolerance is None else tolerance)
+        mi = C.c_uint32(int(max_iterations))
+        if _is_cuda(Y):
+            import torch
+            Y = _as_torch(Y)
+            want = torch.float32 if self.dtype == np.float32 else torch.float64
+            if Y.dtype != want or Y.ndim != 2 or Y.shape[1] != self.shape[0] or Y.device.index != self.devices[0]:
+                raise ValueError(f"signals must be a (batch, {self.shape[0]}) {want} tensor on cuda:{self.devices[0]}")
+            Y = Y.contiguous()
+            B = Y.shape[0]
+            with torch.cuda.device(self.devices[0]):
+                X = torch.empty((B, self.shape[1]), dtype=Y.dtype, device=Y.device)
+                iters = torch.empty(B, dtype=torch.int32, device=Y.device)
+                errs = torch.empty(B, dtype=torch.float64, device=Y.device)
+                check(getattr(lib(), f"ssb200_group_solve_batch_dev_{self._sfx}")(
+                    self._g, C.c_void_p(Y.data_ptr()), C.c_size_t(B), C.c_size_t(self.shape[0]), tol, mi, C.c_void_p(X.data_ptr()),
+                    C.c_size_t(self.shape[1]), C.c_void_p(iters.data_ptr()), C.c_void_p(errs.data_ptr()),
+                    C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            return X, iters, errs
+        if not isinstance(Y, np.ndarray) or Y.dtype != self.dtype:
+            raise TypeError(f"signals must be a numpy array of dtype {self.dtype}")
+        if Y.ndim != 2 or Y.shape[1] != self.shape[0]:
+            raise ValueError(f"signals must be (batch, {self.shape[0]})")
+        Y = np.ascontiguousarray(Y)
+        B = Y.shape[0]
+        X = np.empty((B, self.shape[1]), dtype=self.dtype)
+        iters = np.empty(B, dtype=np.uint32)
+        errs = np.empty(B, dtype=np.float64)
+        check(getattr(lib(), f"ssb200_group_solve_batch_{self._sfx}")(
+            self._g, _ptr(Y), C.c_size_t(B), C.c_size_t(self.shape[0]), tol, mi, _ptr(X), C.c_size_t(self.shape[1]), _ptr(iters), _ptr(errs)))
+        return X, iters, errs
 
 
 class Irls(_Solver):

@@ -1,4 +1,6 @@
 """Helpers shared by the -m gpu parity tests."""
+import os
+
 import numpy as np
 
 import parity
@@ -6,6 +8,43 @@ import parity
 
 def c0_inf(A, Y):
     return np.abs(np.asarray(Y, dtype=np.float64) @ np.asarray(A, dtype=np.float64)).max(axis=1)
+
+
+def have_ref():
+    from oracle import ref
+    return ref.available() and os.path.exists("/root/repo/oracle/_ref/libcblas_fwd.so")
+
+
+def cpu_reference(A, Y, tol, max_iter):
+    """(X, iters, errs) of the reference's CPU path on these inputs: the UNMODIFIED reference build (oracle/_ref, present
+    on the GPU box) when it is there, else the plain-C restatement.  Second value: which one."""
+    from oracle import port, ref
+    if have_ref():
+        ref.set_blas_threads(1)
+        return ref.homotopy(A, Y, tol, max_iter, threads=len(os.sched_getaffinity(0))), "ref"
+    return port.homotopy(A, Y, tol, max_iter), "port"
+
+
+def cpu_floor(A, Y, tol, max_iter, primary):
+    """Mismatch counts of the two CPU builds against each other on these inputs (float32 noise floor of the gate);
+    None when only one of them is at hand."""
+    if not have_ref() or np.dtype(A.dtype) != np.dtype(np.float32):
+        return None
+    from oracle import port
+    Xp, itp, ep = port.homotopy(A, Y, tol, max_iter)
+    return parity.counts(parity.compare(Xp, itp, ep, primary[0], primary[1], primary[2], c0_inf(A, Y)))
+
+
+def check_against_cpu(solver, A, Y, tol, max_iter, what, noise_rate=0.02):
+    """The parity gate against the reference build (the restatement where that is absent), held to the floor the two CPU
+    builds show against each other on the same inputs.  Returns (counts, floor, (X, iters, errs), (Xr, itr, er))."""
+    primary, who = cpu_reference(A, Y, tol, max_iter)
+    floor = cpu_floor(A, Y, tol, max_iter, primary)
+    X, it, err = solver.solve_batch(Y, tol, max_iter)
+    r = parity.compare(X, it, err, primary[0], primary[1], primary[2], c0_inf(A, Y))
+    c = parity.assert_parity(r, A.dtype, f"{what} [vs {who}]", noise_rate=noise_rate, floor=floor)
+    print(f"PARITY {what} vs {who}: {c} floor(port vs ref): {floor}")
+    return c, floor, (X, it, err), primary
 
 
 def check_homotopy(solver, A, Y, tol, max_iter, Xr, itr, er, what, noise_rate=0.02):

@@ -40,24 +40,44 @@ def compare(X, iters, errs, Xr, itr, er, c0_inf=None):
     )
 
 
-def assert_parity(r, dtype, what="", noise_rate=0.02):
-    """The gate.  float64: everything exact / within 1e-10.  float32: the same gate, but a signal may
-    sit at the oracle-vs-oracle noise floor (two CPU builds of the same source disagree on ~1 % of
-    f32 signals): at most `noise_rate` of the signals may show a rounding-level iter
-    flip, a soft support flip or a coefficient error in (1e-4, 1e-3]; nothing may exceed that."""
+def counts(r):
+    """Mismatch counts of one compare(): everything but `iter` over the signals whose iteration counts agree."""
+    good = ~r["iter"]
+    return dict(n=int(len(good)), iter=int(r["iter"].sum()), support=int((r["support"] & good).sum()),
+                soft=int((r["support_soft"] & good).sum()), coef=int((r["coef"] & good).sum()), err=int((r["err"] & good).sum()),
+                coef_max=float(r["coef_rel"][good].max()) if good.any() else 0.0)
+
+
+def allowance(floor_count):
+    """How many mismatches a float32 comparison may show when two CPU builds of the reference show `floor_count` on the very
+    same inputs: the same rate, 3 sigma of the difference of two Poisson counts, + 1."""
+    return int(floor_count + np.ceil(3.0 * np.sqrt(2.0 * max(floor_count, 1))) + 1)
+
+
+def assert_parity(r, dtype, what="", noise_rate=0.02, floor=None):
+    """The gate.  float64: everything exact / within 1e-10.  float32: the same gate, but two CPU builds of the SAME reference
+    source (OpenBLAS vs plain loops, or two OpenBLAS versions) already disagree on a few per cent of the signals at rounding
+    level (profiles/r2_parity.json), so the GPU is held to that measured floor, not to zero:
+      floor  counts() of the CPU-against-CPU comparison on these very inputs: each class of mismatch may occur allowance(floor)
+             times -- the rate the two CPU builds show, plus a 3-sigma margin;
+      noise_rate  used when no second CPU build is at hand: that fraction of the signals per class.
+    Hard support mismatches and coefficient errors above 1e-3 are never allowed beyond what the floor itself shows."""
     n = len(r["iter"])
     f32 = np.dtype(dtype) == np.dtype(np.float32)
-    allow = int(np.ceil(noise_rate * n)) if f32 else 0
-    n_iter = int(r["iter"].sum())
-    assert n_iter <= allow, f"{what}: {n_iter}/{n} iteration-count mismatches"
+    c = counts(r)
     good = ~r["iter"]
-    assert not r["support"][good].any(), f"{what}: hard support mismatch at {np.nonzero(r['support'] & good)[0][:8]}"
-    n_soft = int(r["support_soft"][good].sum())
-    assert n_soft <= allow, f"{what}: {n_soft}/{n} soft support flips"
-    n_coef = int(r["coef"][good].sum())
-    assert n_coef <= allow, f"{what}: {n_coef}/{n} coefficient mismatches, max rel {r['coef_rel'][good].max():.3g}"
-    if f32:
-        assert r["coef_rel"][good].max() <= 1e-3, f"{what}: max rel coef err {r['coef_rel'][good].max():.3g}"
-    n_err = int(r["err"][good].sum())
-    assert n_err <= allow, f"{what}: {n_err}/{n} solution_error mismatches"
-    return dict(iter=n_iter, soft=n_soft, coef=n_coef, err=n_err, n=n)
+
+    def allow(key):
+        if not f32:
+            return 0
+        return allowance(floor[key]) if floor is not None else int(np.ceil(noise_rate * n))
+    assert c["iter"] <= allow("iter"), f"{what}: {c['iter']}/{n} iteration-count mismatches (allowed {allow('iter')})"
+    hard_ok = floor["support"] if (floor is not None and f32) else 0
+    assert c["support"] <= hard_ok, f"{what}: hard support mismatch at {np.nonzero(r['support'] & good)[0][:8]} (floor {hard_ok})"
+    assert c["soft"] <= allow("soft"), f"{what}: {c['soft']}/{n} soft support flips (allowed {allow('soft')})"
+    assert c["coef"] <= allow("coef"), f"{what}: {c['coef']}/{n} coefficient mismatches (allowed {allow('coef')}), max rel {c['coef_max']:.3g}"
+    if f32 and good.any():
+        lim = max(1e-3, floor["coef_max"] * 2) if floor is not None else 1e-3
+        assert c["coef_max"] <= lim, f"{what}: max rel coef err {c['coef_max']:.3g}"
+    assert c["err"] <= allow("err"), f"{what}: {c['err']}/{n} solution_error mismatches (allowed {allow('err')})"
+    return c

@@ -19,7 +19,9 @@ def _declared_symbols():
 def test_header_declares_the_reference_boundary():
     syms = _declared_symbols()
     for need in ("ssb200_homotopy_create_f32", "ssb200_homotopy_solve_f64", "ssb200_homotopy_solve_batch_f32",
-                 "ssb200_irls_create_f64", "ssb200_irls_solve_batch_f32", "ssb200_destroy", "ssb200_last_error"):
+                 "ssb200_irls_create_f64", "ssb200_irls_solve_batch_f32", "ssb200_destroy", "ssb200_last_error",
+                 "ssb200_group_create_f32", "ssb200_group_solve_batch_f32", "ssb200_group_solve_batch_dev_f64", "ssb200_group_destroy",
+                 "ssb200_homotopy_set_residual_mode", "ssb200_homotopy_get_residual_info"):
         assert need in syms
 
 
@@ -57,6 +59,8 @@ def test_no_device_fails_loudly_no_cpu_fallback():
         ss.Homotopy(np.eye(5, dtype=np.float32))
     with pytest.raises(ss.SolverError, match="Compute Mode Unavailable"):
         ss.Irls(np.eye(5, dtype=np.float64))
+    with pytest.raises(ss.SolverError, match="Compute Mode Unavailable"):
+        ss.HomotopyGroup(np.eye(5, dtype=np.float32), devices=[0, 1])
 
 
 def test_product_never_imports_the_oracle():

@@ -31,11 +31,10 @@ def test_cuda_signals_equal_host_path(case):
 
 def test_oracle_parity_through_the_device_front_end(case):
     import torch
-    from oracle import port
     import parity
-    from gpu_util import c0_inf
+    from gpu_util import c0_inf, cpu_reference
     ss, A, Y, s, X, it, err = case
-    Xr, itr, er = port.homotopy(A, Y, 1e-3, 40)
+    (Xr, itr, er), _ = cpu_reference(A, Y, 1e-3, 40)
     dX, dit, derr = s.solve_batch(torch.from_numpy(Y).cuda(), 1e-3, 40)
     r = parity.compare(dX.cpu().numpy(), dit.cpu().numpy().astype(np.uint32), derr.cpu().numpy(), Xr, itr, er, c0_inf(A, Y))
     parity.assert_parity(r, np.float32, "device front-end")
