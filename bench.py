@@ -65,6 +65,7 @@ def parse():
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05", "tcgen05-tf32"])
     ap.add_argument("--cpu-sample", type=int, default=None, help="signals in the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cells", default=None, help="GRID: only these cells, e.g. 64x256,256x1024")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true", help="no per-kernel CUDA events in the timed region (roofline absent)")
     ap.add_argument("--gather-x", action="store_true", help="gather the DENSE coefficients instead of the sparse form")
@@ -278,8 +279,11 @@ def run_grid(args, cfg):
     have_ref = (not args.no_cpu_baseline) and ref.available()
     if have_ref:
         ref.set_blas_threads(1)
+    only = None if not args.cells else {tuple(int(v) for v in c.split("x")) for c in args.cells.split(",")}
     for M in Ms:
         for N in Ns:
+            if only is not None and (M, N) not in only:
+                continue
             hay, sig = grid_workload(M, N)
             solver = ss.Homotopy(hay)
             it_gpu, it_ref = np.zeros(solves, dtype=np.int64), np.zeros(solves, dtype=np.int64)

@@ -15,14 +15,33 @@ def have_ref():
     return ref.available() and os.path.exists("/root/repo/oracle/_ref/libcblas_fwd.so")
 
 
+_MEMO = {}
+
+
+def _key(who, A, Y, tol, max_iter):
+    import hashlib
+    return (who, A.shape, str(A.dtype), hashlib.md5(np.ascontiguousarray(A)).hexdigest(), hashlib.md5(np.ascontiguousarray(Y)).hexdigest(),
+            float(tol), int(max_iter))
+
+
+def _cpu(who, A, Y, tol, max_iter):
+    """memoised across test parametrisations (the CPU side is the slow one)"""
+    from oracle import port, ref
+    k = _key(who, A, Y, tol, max_iter)
+    if k not in _MEMO:
+        if who == "ref":
+            ref.set_blas_threads(1)
+            _MEMO[k] = ref.homotopy(A, Y, tol, max_iter, threads=len(os.sched_getaffinity(0)))
+        else:
+            _MEMO[k] = port.homotopy(A, Y, tol, max_iter)
+    return _MEMO[k]
+
+
 def cpu_reference(A, Y, tol, max_iter):
     """(X, iters, errs) of the reference's CPU path on these inputs: the UNMODIFIED reference build (oracle/_ref, present
     on the GPU box) when it is there, else the plain-C restatement.  Second value: which one."""
-    from oracle import port, ref
-    if have_ref():
-        ref.set_blas_threads(1)
-        return ref.homotopy(A, Y, tol, max_iter, threads=len(os.sched_getaffinity(0))), "ref"
-    return port.homotopy(A, Y, tol, max_iter), "port"
+    who = "ref" if have_ref() else "port"
+    return _cpu(who, A, Y, tol, max_iter), who
 
 
 def cpu_floor(A, Y, tol, max_iter, primary):
@@ -30,8 +49,7 @@ def cpu_floor(A, Y, tol, max_iter, primary):
     None when only one of them is at hand."""
     if not have_ref() or np.dtype(A.dtype) != np.dtype(np.float32):
         return None
-    from oracle import port
-    Xp, itp, ep = port.homotopy(A, Y, tol, max_iter)
+    Xp, itp, ep = _cpu("port", A, Y, tol, max_iter)
     return parity.counts(parity.compare(Xp, itp, ep, primary[0], primary[1], primary[2], c0_inf(A, Y)))
 
 

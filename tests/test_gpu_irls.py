@@ -31,6 +31,31 @@ def test_golden(ss, name):
     assert (np.argmax(X[ok], axis=1) == np.argmax(g["X"][ok], axis=1)).all()
 
 
+def test_golden_c4_shape(ss):
+    """BASELINE config 4 at its own size (IRLS float64, 4096 x 1024, the tall reading): outputs of the unmodified reference
+    (tests/golden/make_golden_c4.py, minutes per signal on the CPU: irls-cpu.cpp:72-73 re-forms Q and R inside every solve).
+    The 32 MB dictionary is regenerated from the seed and checked against the stored checksums first."""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    from make_golden_c4 import inputs
+    g = np.load(os.path.join(GOLDEN, "irls_f64_4096x1024_k64_c4.npz"))
+    A, Y = inputs(int(g["batch"]), int(g["seed"]), int(g["m"]), int(g["n"]), int(g["k"]))
+    assert A.sum() == float(g["a_sum"]) and np.abs(A).sum() == float(g["a_abs"]) and Y.sum() == float(g["y_sum"]), "inputs did not regenerate bit for bit"
+    X, it, err, spd = ss.Irls(A).solve_batch(Y, float(g["tol"]), int(g["max_iter"]))
+    print("C4 golden: iters", it, "spd", spd.astype(int), "eps", err, "reference eps", g["errs"])
+    assert (it == g["iters"]).all() and (spd == g["spd"]).all()
+    np.testing.assert_allclose(err, g["errs"], rtol=1e-10)          # float64 path: the north star's 1e-10
+    ok = ~np.isnan(g["X"]).any(axis=1)
+    assert (np.isnan(X).any(axis=1) == ~ok).all()
+    dev = np.abs(X[ok] - g["X"][ok]).max(axis=1) / np.abs(g["X"][ok]).max(axis=1)
+    print("C4 golden: max coefficient deviation relative to max|x|:", dev)
+    # The last iteration solves a system whose SPD test is about to fail (every one of these solves ends on spd_failure), so
+    # the coefficients carry its conditioning: on the first two of these signals the reference build and its plain-C
+    # restatement (767 s on the CPU) agree on iters / spd / eps to 3e-15 and on x to 8.5e-6 and 2.2e-6 of max|x| only.
+    assert (dev <= 1e-4).all()
+    assert (np.argmax(X[ok], axis=1) == np.argmax(g["X"][ok], axis=1)).all()
+
+
 @pytest.mark.parametrize("dtype,m,n,k", [(np.float64, 96, 24, 2), (np.float64, 200, 64, 1), (np.float32, 80, 20, 1),
                                           (np.float64, 700, 200, 3), (np.float32, 300, 130, 2)])   # several Gram / Cholesky tiles
 def test_vs_port(ss, dtype, m, n, k):

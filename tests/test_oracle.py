@@ -209,3 +209,15 @@ def test_port_vs_reference_irls():
     X, it, e, s = port.irls(A, Y, 1e-3, 50)
     assert (it == itr).all() and (s == sr).all()
     np.testing.assert_allclose(e, er, rtol=1e-6)
+
+
+@needs_ref
+def test_reference_norm_l1_and_reconstruct_known_answers():
+    """src/linalg/norms_test.cpp:9-24 through the reference's public ss::norm_l1, and y = A x through ss::reconstruct_signal
+    (include/ss/ss.h:79-93): pins the oracle/_ref entry points the GPU utilities are tested against."""
+    from oracle import ref
+    A = np.array([[1, 2, 0], [3, 4, 1]], dtype=np.float32)
+    np.testing.assert_allclose(ref.norm_l1(A), [[0.25, 0.3333, 0], [0.75, 0.6667, 1]], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(ref.reconstruct_signal(A, np.array([1, 1, 1], dtype=np.float32)), [3, 8])
+    Ad = np.arange(12, dtype=np.float64).reshape(3, 4)
+    np.testing.assert_allclose(ref.reconstruct_signal(Ad, np.array([1.0, 0, -1, 2])), Ad @ np.array([1.0, 0, -1, 2]))
