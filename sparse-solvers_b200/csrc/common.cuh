@@ -70,6 +70,13 @@ template <> struct num_traits<double> { static __host__ __device__ double max() 
 // ---- device reductions ----------------------------------------------------------------------
 #ifdef __CUDACC__
 
+// separately rounded multiply / add: keeps nvcc from contracting them into an FMA where the reference's build (x86-64
+// baseline, no FMA instruction) rounds twice and an EXACT outcome depends on it
+__device__ __forceinline__ float  mul_rn(float a, float b)   { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float  add_rn(float a, float b)   { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+
 // (value, index) candidates ordered lexicographically: smaller value first, then lower index --
 // the left-most strict decrease of the reference's scan (homotopy-cpu.cpp:156-160).
 template <typename T>

@@ -221,21 +221,23 @@ static void launch_scan(int threads, int nch, bool gram, unsigned grid, cudaStre
 {
 #define SSB_SCAN(TH, NC)                                                                          \
     if (threads == TH && nch == NC) {                                                             \
-        if (gram) homotopy_scan_kernel<T, TH, NC, true><<<grid, TH, 0, st>>>(a, kb);              \
-        else      homotopy_scan_kernel<T, TH, NC, false><<<grid, TH, 0, st>>>(a, kb);             \
+        if (a.exact) { if (gram) homotopy_scan_kernel<T, TH, NC, true, true><<<grid, TH, 0, st>>>(a, kb);     \
+                       else      homotopy_scan_kernel<T, TH, NC, false, true><<<grid, TH, 0, st>>>(a, kb); } \
+        else         { if (gram) homotopy_scan_kernel<T, TH, NC, true, false><<<grid, TH, 0, st>>>(a, kb);    \
+                       else      homotopy_scan_kernel<T, TH, NC, false, false><<<grid, TH, 0, st>>>(a, kb); } \
         SSB_CUDA(cudaGetLastError()); return; }
     SSB_SCAN(128, 1) SSB_SCAN(128, 2) SSB_SCAN(128, 4) SSB_SCAN(256, 1) SSB_SCAN(256, 2) SSB_SCAN(256, 4) SSB_SCAN(256, 0)
 #undef SSB_SCAN
     throw invalid_argument{ "no scan-kernel variant for this shape" };
 }
 
-template <typename T, int W>
+template <typename T, int W, bool EXACT>
 static void launch_algebra_variant(unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
     static std::atomic<uint64_t> configured{ 0 };
     const size_t smem = slice * W;
-    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_algebra_kernel<T, W>, configured);
-    homotopy_algebra_kernel<T, W><<<(rows + W - 1) / W, W * 32, smem, st>>>(a, kb, ks, (int)slice);
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_algebra_kernel<T, W, EXACT>, configured);
+    homotopy_algebra_kernel<T, W, EXACT><<<(rows + W - 1) / W, W * 32, smem, st>>>(a, kb, ks, (int)slice);
     SSB_CUDA(cudaGetLastError());
 }
 
@@ -252,9 +254,15 @@ static inline int algebra_warps(size_t slice) {
 template <typename T>
 static void launch_algebra(int W, unsigned rows, size_t slice, cudaStream_t st, const HomArgs<T>& a, int kb, int ks)
 {
-    if (W == 4) launch_algebra_variant<T, 4>(rows, slice, st, a, kb, ks);
-    else if (W == 2) launch_algebra_variant<T, 2>(rows, slice, st, a, kb, ks);
-    else launch_algebra_variant<T, 1>(rows, slice, st, a, kb, ks);
+    if (a.exact) {
+        if (W == 4) launch_algebra_variant<T, 4, true>(rows, slice, st, a, kb, ks);
+        else if (W == 2) launch_algebra_variant<T, 2, true>(rows, slice, st, a, kb, ks);
+        else launch_algebra_variant<T, 1, true>(rows, slice, st, a, kb, ks);
+        return;
+    }
+    if (W == 4) launch_algebra_variant<T, 4, false>(rows, slice, st, a, kb, ks);
+    else if (W == 2) launch_algebra_variant<T, 2, false>(rows, slice, st, a, kb, ks);
+    else launch_algebra_variant<T, 1, false>(rows, slice, st, a, kb, ks);
 }
 
 

@@ -562,12 +562,16 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         // the winning join step again, in IEEE arithmetic (the ordering used the hardware reciprocal)
         if (sh_join && !present && !SSB_IEEE_ORDER) {
             if constexpr (NCH > 0) {
+                if ((uint32_t)tid == (idx / V) % THREADS) {   // the thread that holds atom idx: selects, then ONE pair of divisions
+                    T cw = T(0), qw = T(0);
 #pragma unroll
-                for (int ch = 0; ch < NCH; ++ch) {
-                    const int i0 = (ch * THREADS + tid) * V;
+                    for (int ch = 0; ch < NCH; ++ch) {
+                        const int i0 = (ch * THREADS + tid) * V;
 #pragma unroll
-                    for (int e = 0; e < V; ++e)
-                        if ((uint32_t)(i0 + e) == idx) sh_gamma = winning_step(lam, cv[ch][e], qv[ch][e], sh_gamma);
+                        for (int e = 0; e < V; ++e)
+                            if ((uint32_t)(i0 + e) == idx) { cw = cv[ch][e]; qw = qv[ch][e]; }
+                    }
+                    sh_gamma = winning_step(lam, cw, qw, sh_gamma);
                 }
             } else if (tid == 0) sh_gamma = winning_step(lam, csrc[idx], q[idx], sh_gamma);
             __syncthreads();   // sh_join and present are block-uniform
@@ -595,11 +599,16 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         if (a.exact && tid == 0) s_x[K] = x[idx];   // 0, or the rounding residue of an atom that left earlier
     }
 
-    // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
+    // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0.  Multiply and add are
+    // rounded separately, as in the reference's build: the leaving atom's x + fl(gamma d) with gamma = fl(-x / d) is then
+    // EXACTLY zero most of the time, where a fused multiply-add leaves the division's rounding error behind almost always --
+    // and a non-zero residue of the "wrong" sign makes the atom leave again the moment it rejoins (:129-137), after which it
+    // sits outside the active set with the largest |c| and the solve runs to max_iterations (measured on the reference's own
+    // bench workload: 12 of 32 solves with the fused form against 3 of 32 for the reference, tests/studies/)
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
-        if (k < K) { const T xn = xk[u] + gamma * s_d[k]; x[s_gam[k]] = xn; if (a.exact) s_x[k] = xn; }
+        if (k < K) { const T xn = add_rn(xk[u], mul_rn(gamma, s_d[k])); x[s_gam[k]] = xn; if (a.exact) s_x[k] = xn; }
     }
 
     // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270).  Exact mode: c is this iteration's fresh

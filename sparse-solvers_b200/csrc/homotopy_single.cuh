@@ -265,8 +265,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
 
         if (cta == 0) {
             const int ldm = a.ks;
-            // x += gamma * d with the OLD direction (:252)
-            for (int k = tid; k < K; k += THREADS) { const T xv = s_x[k] + gamma * s_d[k]; s_x[k] = xv; a.x[s_gam[k]] = xv; }
+            // x += gamma * d with the OLD direction (:252), multiply and add rounded separately (see homotopy_scan_kernel)
+            for (int k = tid; k < K; k += THREADS) { const T xv = add_rn(s_x[k], mul_rn(gamma, s_d[k])); s_x[k] = xv; a.x[s_gam[k]] = xv; }
             int slot = -1;
             if (present) { for (int k = 0; k < K; ++k) if (s_gam[k] == idx) slot = k; }
             const int ncg = K + (present ? 0 : 1);

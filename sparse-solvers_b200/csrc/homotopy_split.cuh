@@ -37,7 +37,7 @@ __device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
 //   GRAMQ  q is not read from the contraction's output but formed here as q = G[:, active] d (G = A^T A, L2-resident): while
 //          the active set is small that is K rows of G per signal instead of a full 2 M N contraction, a gather of K atoms
 //          and 16 KB of Q traffic -- the host uses it for the first iterations (K <= it < gram_iters)
-template <typename T, int THREADS, int NCH, bool GRAMQ>
+template <typename T, int THREADS, int NCH, bool GRAMQ, bool EXACT>
 __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a, int kb)
 {
     constexpr int GRAM_KMAX = 32;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     const T* q = a.Q + (size_t)pos * a.ldc;
     // exact mode: the search reads this iteration's fresh c' -- the contraction's second row block, or, on a Gram iteration,
     // c0 - G_G x_G formed below from the same rows of G that give q
-    const T* csrc = a.exact ? (GRAMQ ? a.C0 + (size_t)s * a.ldc : a.Qc + (size_t)pos * a.ldc) : c;
+    const T* csrc = EXACT ? (GRAMQ ? a.C0 + (size_t)s * a.ldc : a.Qc + (size_t)pos * a.ldc) : c;
     T* x = a.X + (size_t)s * a.ldx;
     const uint32_t* maskg = a.mask + (size_t)s * (a.ldc >> 5);
     const T TMAX = num_traits<T>::max();
@@ -98,7 +98,6 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     if constexpr (GRAMQ && NCH > 0) {
         if (tid < kb) { s_gq[tid] = gk[0]; s_dq[tid] = dk[0]; if (tid < K) s_xq[tid] = xk[0]; }   // kb <= GRAM_KMAX <= THREADS (checked by the host)
         __syncthreads();
-        const bool ex = a.exact != 0;
 #pragma unroll
         for (int ch = 0; ch < NCH; ++ch) {
             const int i0 = (ch * THREADS + tid) * V;
@@ -113,7 +112,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
                     const T d = s_dq[k];
 #pragma unroll
                     for (int e = 0; e < V; ++e) qv[ch][e] += gv[e] * d;
-                    if (ex) {   // c' = A^T y - G_G x_G, re-formed every iteration
+                    if constexpr (EXACT) {   // c' = A^T y - G_G x_G, re-formed every iteration
                         const T xg = s_xq[k];
 #pragma unroll
                         for (int e = 0; e < V; ++e) cv[ch][e] -= gv[e] * xg;
@@ -121,7 +120,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
                 }
         }
     }
-    if (a.exact) {   // lambda = |c'|_inf over the vector the search reads (:270 on the re-formed c)
+    if constexpr (EXACT) {   // lambda = |c'|_inf over the vector the search reads (:270 on the re-formed c)
         T mx0 = T(0);
         if constexpr (NCH > 0) {
 #pragma unroll
@@ -221,12 +220,16 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         // the winning join step again, in IEEE arithmetic (the ordering used the hardware reciprocal)
         if (sh_join && !SSB_IEEE_ORDER) {
             if constexpr (NCH > 0) {
+                if ((uint32_t)tid == (idx / V) % THREADS) {   // the thread that holds atom idx: selects, then ONE pair of divisions
+                    T cw = T(0), qw = T(0);
 #pragma unroll
-                for (int ch = 0; ch < NCH; ++ch) {
-                    const int i0 = (ch * THREADS + tid) * V;
+                    for (int ch = 0; ch < NCH; ++ch) {
+                        const int i0 = (ch * THREADS + tid) * V;
 #pragma unroll
-                    for (int e = 0; e < V; ++e)
-                        if ((uint32_t)(i0 + e) == idx) sh_gamma = winning_step(lam, cv[ch][e], qv[ch][e], sh_gamma);
+                        for (int e = 0; e < V; ++e)
+                            if ((uint32_t)(i0 + e) == idx) { cw = cv[ch][e]; qw = qv[ch][e]; }
+                    }
+                    sh_gamma = winning_step(lam, cw, qw, sh_gamma);
                 }
             } else if (tid == 0) sh_gamma = winning_step(lam, csrc[idx], q[idx], sh_gamma);
             __syncthreads();   // sh_join is block-uniform
@@ -239,11 +242,16 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         return;
     }
 
-    // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0
+    // ---- x += gamma * d with the OLD direction (:252): a leaving atom lands on ~0, a joining one stays 0.  Multiply and add are
+    // rounded separately, as in the reference's build: the leaving atom's x + fl(gamma d) with gamma = fl(-x / d) is then
+    // EXACTLY zero most of the time, where a fused multiply-add leaves the division's rounding error behind almost always --
+    // and a non-zero residue of the "wrong" sign makes the atom leave again the moment it rejoins (:129-137), after which it
+    // sits outside the active set with the largest |c| and the solve runs to max_iterations (measured on the reference's own
+    // bench workload: 12 of 32 solves with the fused form against 3 of 32 for the reference, tests/studies/)
 #pragma unroll
     for (int u = 0; u < KR; ++u) {
         const int k = tid + u * THREADS;
-        if (k < K) x[gk[u]] = xk[u] + gamma * dk[u];
+        if (k < K) x[gk[u]] = add_rn(xk[u], mul_rn(gamma, dk[u]));
     }
 
     // ---- c = A^T (y - A x)  ==  c - gamma * q ;  lambda = |c|_inf (:255, :270); exact mode: one step from the fresh c'
@@ -291,7 +299,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
 
 // One warp per continuing signal (row of act_next).  K <= kb before the toggle; the inverse is staged in the warp's
 // shared-memory slice with the odd row stride ks (lane = row: conflict-free), worked on, and written back.
-template <typename T, int W>
+template <typename T, int W, bool EXACT>
 __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, int kb, int ks, int slice_bytes)
 {
     constexpr int V = 16 / sizeof(T);
@@ -436,7 +444,7 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
     // ---- p = A_G d for the next contraction (:112-116), k ascending per element as in write_rhs; in exact mode also the
     // residual r = y - A_G x_G (:94-96 over the active atoms) from the same atom rows
     if (a.skip_rhs) return;   // the next iteration forms q (and c') from the Gram matrix: no right-hand side needed
-    const bool res = a.exact != 0;
+    constexpr bool res = EXACT;
     T* s_x = s_u2;            // free since the inverse update
     if (res) {
         const T* x = a.X + (size_t)s * a.ldx;

@@ -33,11 +33,7 @@ struct IrlsArgs {
     T tol; uint32_t max_iter;
 };
 
-// separately rounded multiply / add: keeps nvcc from contracting them into an FMA the reference's build does not use
-__device__ __forceinline__ float  mul_rn(float a, float b)   { return __fmul_rn(a, b); }
-__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
-__device__ __forceinline__ float  add_rn(float a, float b)   { return __fadd_rn(a, b); }
-__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+// (mul_rn / add_rn, common.cuh: separately rounded multiply / add -- an FMA is something the reference's build does not use)
 
 template <typename T, int THREADS>
 __device__ __forceinline__ T block_sum(T v, T* red) {

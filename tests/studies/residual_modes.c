@@ -14,6 +14,12 @@
  *                            stop test and the report use  c' - gamma q  (one step from a fresh base, never accumulated)
  *   mode 5  Gram form:       c = A^T y - G_G x_G,  q = G_G d  with G = fl(A^T A)
  *   mode 6  mixed:           mode 5 while iter < switch_iter, mode 4 from then on      (what the lockstep path does)
+ *   mode 8  mode 0 with the x update FUSED, x = fma(gamma, d, x): what a GPU compiler makes of `x += gamma * d` by default.  The
+ *           reference's build rounds the product and the sum separately, which leaves a LEAVING atom's coefficient at exactly
+ *           zero most of the time; fused, the division's rounding error stays behind, and when its sign is "wrong" the atom
+ *           is thrown out again the moment it rejoins, stays outside the active set with the largest |c| -- and the solve stalls
+ *   mode 7  mode 4 with the step candidates ORDERED by an approximate quotient num * (1/den) (two roundings, like the GPU's
+ *           reciprocal-based __fdividef) and the winning step then recomputed with IEEE division
  *
  * Build: gcc -O2 -fopenmp -o tests/studies/_build/residual_modes tests/studies/residual_modes.c -lm
  * Driver: tests/studies/residual_modes.py
@@ -86,7 +92,7 @@ uint32_t solve_mode(int mode, int switch_iter, const float* A, const float* G, s
     uint32_t iter = 0;
     do {
         iter++;
-        const int md = mode == 6 ? ((int)iter < switch_iter ? 5 : 4) : mode;
+        const int md = mode == 6 ? ((int)iter < switch_iter ? 5 : 4) : mode == 7 ? 4 : mode == 8 ? 0 : mode;
         float min; size_t idx;
         const float* csearch = c;
         float lam_search = c_inf;
@@ -117,6 +123,33 @@ uint32_t solve_mode(int mode, int switch_iter, const float* A, const float* G, s
                 if (prev > mn) ix = i;
             }
             min = mn; idx = ix;
+        } else if (mode == 7) {
+            /* p, q as find_max_gamma; candidates ordered by num * (1 / den), the winner's step in IEEE arithmetic */
+            for (size_t i = 0; i < m; ++i) {
+                float acc = 0;
+                for (size_t k = 0; k < lam.n; ++k) { size_t j = lam.v[k]; acc += A_(i, j) * direction[j]; }
+                p[i] = acc;
+            }
+            correlate(A, m, n, p, q);
+            float mn = FLT_MAX; size_t ix = 0, l = 0; int join = 0;
+            for (size_t i = 0; i < n; ++i) {
+                const float prev = mn;
+                if (l < lam.n && lam.v[l] == i) { float t = -x[i] / direction[i]; if (t > 0.0 && t < mn) { mn = t; join = 0; } l++; }
+                else {
+                    float dl = 1.0f - q[i], dr = 1.0f + q[i];
+                    volatile float rl = 1.0f / dl, rr = 1.0f / dr;
+                    if (dl != 0.0) { float t = (lam_search - csearch[i]) * rl; if (t > 0.0 && t < mn) { mn = t; join = 1; } }
+                    if (dr != 0.0) { float t = (lam_search + csearch[i]) * rr; if (t > 0.0 && t < mn) { mn = t; join = 1; } }
+                }
+                if (prev > mn) ix = i;
+            }
+            if (join && mn < FLT_MAX) {
+                float best = FLT_MAX, dl = 1.0f - q[ix], dr = 1.0f + q[ix];
+                if (dl != 0.0) { float t = (lam_search - csearch[ix]) / dl; if (t > 0.0 && t < best) best = t; }
+                if (dr != 0.0) { float t = (lam_search + csearch[ix]) / dr; if (t > 0.0 && t < best) best = t; }
+                if (best < FLT_MAX) mn = best;
+            }
+            min = mn; idx = ix;
         } else {
             /* find_max_gamma with the chosen search vector (it forms p and q itself) */
             find_max_gamma_f32(A, m, n, rs, cst, csearch, x, direction, lam_search, &lam, p, q, &min, &idx);
@@ -124,7 +157,8 @@ uint32_t solve_mode(int mode, int switch_iter, const float* A, const float* G, s
         inverse_add_or_remove_f32(A, m, rs, cst, idx, &lam, &inv, colbuf);
         size_t K = lam.n;
         if (K == 0) break;
-        for (size_t j = 0; j < n; ++j) x[j] += min * direction[j];
+        if (mode == 8) for (size_t j = 0; j < n; ++j) x[j] = fmaf(min, direction[j], x[j]);
+        else for (size_t j = 0; j < n; ++j) x[j] += min * direction[j];
         switch (md) {
         case 0: residual_vector_f32(A, m, n, rs, cst, y, x, c, r); break;
         case 1: for (size_t j = 0; j < n; ++j) c[j] = c[j] - min * q[j]; break;

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 HERE = os.path.dirname(os.path.abspath(__file__))
 MODES = {0: "reference form", 1: "incremental c", 2: "incremental r", 3: "active-set r", 4: "stacked (fresh c', one-step signs)",
-         5: "Gram form", 6: "Gram form < 16, stacked from 16"}
+         5: "Gram form", 6: "Gram form < 16, stacked from 16", 7: "stacked, reciprocal-ordered candidates", 8: "reference form, FUSED x update"}
 
 
 def lib():
