@@ -241,6 +241,25 @@ def run_irls(args, cfg):
     iters = float(it.mean()) + float(spd.mean())     # a failing iteration still forms and factors G
     flops = (1.0 * N * N * M + N ** 3 / 3.0) * iters * batch * args.steps     # mul+add pairs counted as 2: N^2/2*M*2 + N^3/6*2
     value = batch * args.steps / secs
+    # FP64 peak measured on this device (ssb200_fp64_peak_probe): independent DFMA chains and mma.sync.m8n8k4.f64 tiles.  The solve
+    # kernel rounds every multiply and add separately (it has to reproduce the reference's SPD verdicts), so it cannot use FMA: its
+    # ceiling is HALF the DFMA peak, which is the denominator used here.
+    dfma, dmma = ss.fp64_peak("dfma"), ss.fp64_peak("dmma")
+    peak = dfma / 2.0
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import ref
+        if ref.available():
+            threads = host_threads()
+            sample = args.cpu_sample or min(8, threads)
+            ref.set_blas_threads(1)
+            t1 = time.perf_counter()
+            Xr, itr, er, sr = ref.irls(A, Y[:sample], cfg["tol"], cfg["max_iter"], threads=min(sample, threads))
+            dt = time.perf_counter() - t1
+            cpu = {"value": sample / dt, "unit": "signals/s", "cores": min(sample, threads), "kind": "reference",
+                   "sample": f"first {sample} signals, one per host thread x 1 BLAS thread, {dt:.1f} s (the reference re-forms Q and R inside every solve, irls-cpu.cpp:72-73)",
+                   "iters_match_gpu": int((itr == it[:sample]).sum()), "spd_failure_match_gpu": int((sr == spd[:sample]).sum()),
+                   "solution_error_max_rel_dev": float(np.max(np.abs(er - err[:sample]) / np.abs(er)))}
     line = {"metric": "irls signals/sec", "value": value, "unit": "signals/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
@@ -248,10 +267,11 @@ def run_irls(args, cfg):
                        "mean_iters": float(it.mean()), "spd_failure_frac": float(spd.mean())},
             "e2e": {"value": value, "unit": "signals/s", "h2d_bytes_per_step": int(Y.nbytes), "d2h_bytes_per_step": int(X.nbytes + it.nbytes + err.nbytes + spd.nbytes)},
             "gpu_launches": solver.counters()["launches"] if hasattr(solver, "counters") else None,
-            "roofline": {"kernel": "irls_solve_kernel (Gram + Cholesky tiles)", "bound": "fp64", "achieved": flops / secs / 1e12, "peak": 40.0,
-                         "unit": "TFLOP/s", "frac": flops / secs / 1e12 / 40.0, "traffic": None,
-                         "peak_source": "B200 FP64 datasheet (no measured FP64 figure in MEASURED_PEAKS.json); separately rounded mul/add cannot use FMA: half of it is the ceiling"},
-            "cpu_baseline": None}
+            "roofline": {"kernel": "irls_solve_kernel (Gram + Cholesky tiles)", "bound": "fp64", "achieved": flops / secs / 1e12, "peak": peak,
+                         "unit": "TFLOP/s", "frac": flops / secs / 1e12 / peak, "traffic": None,
+                         "peak_source": f"measured on this device: DFMA {dfma:.1f} TFLOP/s, DMMA {dmma:.1f} TFLOP/s (ssb200_fp64_peak_probe); separately "
+                                        "rounded mul / add cannot use FMA: half the DFMA figure is the ceiling"},
+            "cpu_baseline": cpu}
     emit(line)
 
 

@@ -114,6 +114,18 @@ int ssb200_homotopy_solve_batch_f32(void* handle, const float* Y, size_t batch, 
 int ssb200_homotopy_solve_batch_f64(void* handle, const double* Y, size_t batch, size_t ldy, double tolerance,
                                     uint32_t max_iterations, double* X, size_t ldx, uint32_t* iters, double* errors);
 
+/* solve_batch with the SPARSE form of the result in host memory (new): row b's non-zero coefficients in index order as
+ * (idx[b*cap + k], val[b*cap + k]) for k < count[b]; entries at k >= count[b] are unspecified.  cap >= min(max_iterations + 1, N),
+ * the most non-zeros a solution can have.  No dense row is formed on the host: 8 (cap) + 16 bytes per signal cross PCIe and are
+ * written once, where the dense form writes 4 N bytes per signal (what bounds the dense entry when several GPUs of one box
+ * return results to the same host memory). */
+int ssb200_homotopy_solve_batch_sparse_f32(void* handle, const float* Y, size_t batch, size_t ldy, float tolerance,
+                                           uint32_t max_iterations, int32_t* idx, float* val, int32_t* count, size_t cap,
+                                           uint32_t* iters, double* errors);
+int ssb200_homotopy_solve_batch_sparse_f64(void* handle, const double* Y, size_t batch, size_t ldy, double tolerance,
+                                           uint32_t max_iterations, int32_t* idx, double* val, int32_t* count, size_t cap,
+                                           uint32_t* iters, double* errors);
+
 int ssb200_homotopy_solve_batch_dev_f32(void* handle, const float* dY, size_t batch, size_t ldy, float tolerance,
                                         uint32_t max_iterations, float* dX, size_t ldx, uint32_t* d_iters,
                                         double* d_errors, void* stream);
@@ -207,9 +219,11 @@ int ssb200_norm_l1_f64(double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrd
  *   counters[3] = lockstep iterations executed
  *   timing (when enabled the contraction launches are bracketed by CUDA events on the handle's
  *   stream):  ms[0] = summed contraction time, ms[1] = summed step-kernel time
- *   path: 0 = choose by batch size (product behaviour), 1 = force the SIMT contraction,
+ *   path: 0 = choose by batch size (product behaviour), 1 = no tcgen05 (float32: register-tiled FFMA; float64: the DMMA kernel),
  *         2 = force the tcgen05 contraction (float32 only; fp16 operand containers, the default flavour),
- *         3 = force the tcgen05 contraction with tf32 operand containers (the literal 3xTF32 scheme)
+ *         3 = force the tcgen05 contraction with tf32 operand containers (the literal 3xTF32 scheme),
+ *         4 = plain FFMA / DFMA tiles for both dtypes (the checker of the tensor-core kernels)
+ *   float64 batches of more than 4 signals run on the FP64 tensor pipe (mma.sync.m8n8k4.f64) by default
  */
 int ssb200_reset_counters(void* handle);
 int ssb200_get_counters(void* handle, uint64_t counters[4]);
@@ -225,6 +239,9 @@ int ssb200_get_kernel_bytes(void* handle, uint64_t bytes[8]);   /* [6] = L2 byte
 /* bytes[0] = host->device, bytes[1] = device->host bytes the host-pointer batch entries copied since the last reset */
 int ssb200_get_transfer_bytes(void* handle, uint64_t bytes[2]);
 int ssb200_set_contraction_path(void* handle, int path);
+/* measured FP64 peak of `device` in TFLOP/s (bench.py's roofline denominator for the float64 paths): kind 0 = independent DFMA
+ * chains on every SM, kind 1 = independent mma.sync.m8n8k4.f64 (DMMA) tiles on every SM */
+int ssb200_fp64_peak_probe(int device, int kind, double* tflops);
 /* test / bench hook for the contraction kernel alone: Q[r][n] = sum_m A[m][n] * P[r][m] for `rows` host rows
  * (P: rows x M, Q: rows x N, both dense row-major), computed by path 1 (SIMT) or 2 (tcgen05, float32);
  * *ms_per_launch = mean device time of `reps` back-to-back launches (CUDA events on the handle's stream). */

@@ -233,6 +233,11 @@ int ssb200_homotopy_solve_batch_##SFX(void* h, const T* Y, size_t batch, size_t 
                                       size_t ldx, uint32_t* iters, double* errs)                                        \
 { return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (Y && X && iters && errs), "null pointer"); \
                        device_guard g(s->device); s->solve_batch_host(Y, batch, ldy, tol, mi, X, ldx, iters, errs); }); } \
+int ssb200_homotopy_solve_batch_sparse_##SFX(void* h, const T* Y, size_t batch, size_t ldy, T tol, uint32_t mi,        \
+                                             int32_t* idx, T* val, int32_t* count, size_t cap, uint32_t* iters, double* errs) \
+{ return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (Y && idx && val && count && iters && errs), "null pointer"); \
+                       device_guard g(s->device); typename Homotopy<T>::SparseOut sp{ idx, val, count, cap };               \
+                       s->solve_batch_host(Y, batch, ldy, tol, mi, nullptr, 0, iters, errs, &sp); }); }                     \
 int ssb200_homotopy_solve_batch_dev_##SFX(void* h, const T* Y, size_t batch, size_t ldy, T tol, uint32_t mi, T* X,      \
                                           size_t ldx, uint32_t* iters, double* errs, void* stream)                      \
 { return guarded([&] { auto* s = as_homotopy<T>(h); SSB_REQUIRE(batch == 0 || (Y && X && iters && errs), "null pointer"); \
@@ -365,7 +370,27 @@ int ssb200_homotopy_get_residual_info(void* h, int* mode_in_effect, double* cohe
                        else { auto* s = static_cast<Homotopy<double>*>(b); ex = s->exact_residual(); mu = s->coherence(); }
                        if (mode_in_effect) *mode_in_effect = ex ? SSB200_RESIDUAL_EXACT : SSB200_RESIDUAL_INCREMENTAL;
                        if (coherence) *coherence = mu; }); }
+int ssb200_fp64_peak_probe(int device, int kind, double* tflops)
+{ return guarded([&] { SSB_REQUIRE(tflops && (kind == 0 || kind == 1), "bad arguments");
+                       require_sm100(device); device_guard g(device);
+                       int sms = 0; SSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+                       const int blocks = sms * 8, iters = 1 << 14;
+                       dev_buffer out; out.reserve((size_t)blocks * 256 * sizeof(double));
+                       cudaEvent_t e0, e1; SSB_CUDA(cudaEventCreate(&e0)); SSB_CUDA(cudaEventCreate(&e1));
+                       float best = 1e30f;
+                       for (int rep = 0; rep < 4; ++rep) {        // first round warms up; best of the rest
+                           SSB_CUDA(cudaEventRecord(e0));
+                           if (kind == 0) fp64_dfma_probe_kernel<<<blocks, 256>>>(out.as<double>(), iters, 1e-3);
+                           else fp64_dmma_probe_kernel<<<blocks, 256>>>(out.as<double>(), iters, 1e-3);
+                           SSB_CUDA(cudaEventRecord(e1)); SSB_CUDA(cudaEventSynchronize(e1));
+                           float ms = 0.f; SSB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+                           if (rep > 0) best = std::min(best, ms);
+                       }
+                       cudaEventDestroy(e0); cudaEventDestroy(e1);
+                       // DFMA: 16 chains x 2 flop per thread-iteration; DMMA: 8 tiles x 512 flop per warp-iteration
+                       const double flop = kind == 0 ? (double)blocks * 256 * iters * 32.0 : (double)blocks * 8 * iters * 8 * 512.0;
+                       *tflops = flop / (best * 1e-3) / 1e12; }); }
 int ssb200_set_contraction_path(void* h, int path)
-{ return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 3, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
+{ return guarded([&] { SSB_REQUIRE(h && path >= 0 && path <= 4, "bad path"); static_cast<SolverBase*>(h)->contraction_path = path; }); }
 
 }  // extern "C"

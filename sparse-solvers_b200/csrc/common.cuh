@@ -3,11 +3,14 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cfloat>
 #include <cstddef>
 #include <cstdint>
 #include <cstdio>
 #include <string>
+
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler injects itself
 
 #include "../../include/ssb200.h"
 
@@ -62,6 +65,25 @@ struct pinned_buffer {
 };
 
 inline size_t round_up(size_t v, size_t to) { return (v + to - 1) / to * to; }
+
+// NVTX range around the launches of one kernel class (contraction / scan / algebra / step): ncu and nsys captures name themselves
+struct nvtx_range {
+    explicit nvtx_range(const char* name) { nvtxRangePushA(name); }
+    ~nvtx_range() { nvtxRangePop(); }
+    nvtx_range(const nvtx_range&) = delete;
+    nvtx_range& operator=(const nvtx_range&) = delete;
+};
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE attribute: one bit per device and kernel instantiation
+inline void optin_shared_memory(const void* fn, std::atomic<uint64_t>& done, int bytes = 200 * 1024)
+{
+    int dev = 0;
+    SSB_CUDA(cudaGetDevice(&dev));
+    const uint64_t bit = 1ull << (dev & 63);
+    if (dev < 64 && (done.load(std::memory_order_acquire) & bit)) return;
+    SSB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done.fetch_or(bit, std::memory_order_release);
+}
 
 template <typename T> struct num_traits;
 template <> struct num_traits<float>  { static __host__ __device__ float  max() { return FLT_MAX; } static __host__ __device__ float  eps() { return FLT_EPSILON; } };

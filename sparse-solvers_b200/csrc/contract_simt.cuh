@@ -11,7 +11,10 @@
 // Q is signal-major [rows][ldq].  Npad % 128 == 0, Mpad % 32 == 0, so no bounds checks on atoms / m.
 #pragma once
 
+#include <cstdlib>
+
 #include "common.cuh"
+#include "contract_dmma.cuh"
 
 namespace ssb {
 
@@ -105,12 +108,30 @@ contract_simt_kernel(const T* __restrict__ At, int lda, const T* __restrict__ P,
     }
 }
 
+// float64 batches go to the FP64 tensor pipe (contract_dmma.cuh) unless the shape rules it out; SSB200_DMMA=0 keeps the
+// register-tiled DFMA kernel (A/B runs, tests/test_gpu_contract.py)
+inline bool dmma_enabled() {
+    static const bool on = [] { const char* e = getenv("SSB200_DMMA"); return !(e && atoi(e) == 0); }();
+    return on;
+}
+
 // returns the number of kernel launches (always 1)
 template <typename T>
 inline int launch_contract_simt(const T* At, int lda, int n_pad, int mdim, const T* P, int ldp, int rows,
-                                T* Q, int ldq, cudaStream_t stream)
+                                T* Q, int ldq, cudaStream_t stream, bool allow_dmma = true)
 {
     if (rows <= 0) return 0;
+    if constexpr (sizeof(T) == 8) {
+        if (rows > 4 && allow_dmma && dmma_enabled() && n_pad % DM_ATOMS == 0 && mdim % DM_BK == 0 && lda % 2 == 0 && ldp % 2 == 0 &&
+            (reinterpret_cast<uintptr_t>(At) & 15) == 0 && (reinterpret_cast<uintptr_t>(P) & 15) == 0) {
+            static std::atomic<uint64_t> configured{ 0 };
+            optin_shared_memory((const void*)contract_dmma_kernel, configured, DM_SMEM_BYTES);
+            dim3 grid(n_pad / DM_ATOMS, (rows + DM_SIGS - 1) / DM_SIGS);
+            contract_dmma_kernel<<<grid, 256, DM_SMEM_BYTES, stream>>>(At, lda, P, ldp, rows, Q, ldq, mdim);
+            SSB_CUDA(cudaGetLastError());
+            return 1;
+        }
+    }
     if (rows <= 4) {
         const int blocks = (n_pad + 7) / 8;  // 8 warps per CTA, one atom per warp
         if (rows == 1)      contract_gemv_kernel<T, 1><<<blocks, 256, 0, stream>>>(At, lda, n_pad, mdim, P, ldp, Q, ldq);

@@ -4,6 +4,8 @@
 // src/solvers/homotopy-cpu.cpp:277-297).
 #pragma once
 
+#include <sched.h>
+
 #include <algorithm>
 #include <atomic>
 #include <exception>
@@ -174,8 +176,11 @@ public:
 
     void solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                          uint32_t* d_iters, double* d_errs, cudaStream_t user_stream);
+    // sparse form of the result on the host: row b's non-zeros in index order as (idx[b * cap + k], val[b * cap + k]), k < count[b]
+    struct SparseOut { int32_t* idx; T* val; int32_t* count; size_t cap; };
+    // X may be null when `sp` is given: the coefficients then come back in the sparse form only (no dense rows are written)
     void solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* X, size_t ldx,
-                          uint32_t* iters, double* errs);
+                          uint32_t* iters, double* errs, const SparseOut* sp = nullptr);
     void reconstruct_host(const T* X, size_t batch, size_t ldx, T* Y, size_t ldy);
     void reconstruct_dev(const T* dX, size_t batch, size_t ldx, T* dY, size_t ldy, cudaStream_t st);
     // test / bench hook: Q[r][n] = sum_m A[m][n] P[r][m] through the chosen contraction kernel, `reps` launches;
@@ -324,7 +329,7 @@ private:
     void check_capacity(int kmax) const;
     bool use_tc(size_t rows) const {
         if (sizeof(T) != 4) return false;
-        if (contraction_path == 1) return false;
+        if (contraction_path == 1 || contraction_path == 4) return false;
         if (!tc_supported(Npad, Mp)) return false;
         if (contraction_path >= 2) return true;
         return rows >= 64;   // below that the tiles are mostly padding and the SIMT kernels win

@@ -32,17 +32,6 @@ void Homotopy<T>::finish_dictionary()
     plan_valid_ = false;
 }
 
-// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE attribute: one bit per device and kernel instantiation
-static inline void optin_shared_memory(const void* fn, std::atomic<uint64_t>& done)
-{
-    int dev = 0;
-    SSB_CUDA(cudaGetDevice(&dev));
-    const uint64_t bit = 1ull << (dev & 63);
-    if (dev < 64 && (done.load(std::memory_order_acquire) & bit)) return;
-    SSB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    done.fetch_or(bit, std::memory_order_release);
-}
-
 template <typename T>
 void Homotopy<T>::check_capacity(int kmax) const
 {
@@ -152,6 +141,7 @@ void Homotopy<T>::reserve_workspace(Lane& L, size_t rows, int kmax)
 template <typename T>
 void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* rows_dev, bool count_rows, int nblk)
 {
+    nvtx_range nv(nblk == 2 ? "ssb200 contraction [Q; C'] = A^T [P; R]" : "ssb200 contraction Q = A^T P");
     const int span = L.begin(timing, 0);
     const size_t prow = (size_t)L.ws_nb * L.ws_rows;          // rows of the P buffers
     if constexpr (sizeof(T) == 4) {
@@ -175,7 +165,7 @@ void Homotopy<T>::contract(Lane& L, bool tc, int which, size_t rows, const int* 
     if (!tc)
         for (int b = 0; b < nblk; ++b)
             L.counters[0] += launch_contract_simt<T>(At_, Mp, Npad, Mp, L.P[which].template as<T>() + (size_t)b * L.ws_rows * Mp, Mp, (int)rows,
-                                                     L.Q.template as<T>() + (size_t)b * L.ws_rows * Npad, Npad, L.stream);
+                                                     L.Q.template as<T>() + (size_t)b * L.ws_rows * Npad, Npad, L.stream, contraction_path != 4);
     L.end(span);
     L.counters[1]++;
     if (count_rows) L.counters[2] += (uint64_t)nblk * rows;
@@ -430,16 +420,16 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         const int span = L.begin(timing, 1);
         if (aw > 0) {
             const int sp_scan = L.begin(timing, gram ? 3 : 2);
-            launch_scan(threads, nch, gram, (unsigned)known, st, a, kb);
+            { nvtx_range nv(gram ? "ssb200 scan (q from Gram rows)" : "ssb200 scan (Q streamed)"); launch_scan(threads, nch, gram, (unsigned)known, st, a, kb); }
             L.end(sp_scan);
             const int sp_alg = L.begin(timing, 4);
-            launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks);
+            { nvtx_range nv("ssb200 algebra"); launch_algebra(aw, (unsigned)known, slice, st, a, kb, ks); }
             L.end(sp_alg);
             L.counters[0] += 2;
             route.push_back(gram ? 3 : 2);
         } else {
             const int sp_step = L.begin(timing, 5);
-            launch_step(threads, nch, gs, (unsigned)known, smem, st, a, kb, ks);
+            { nvtx_range nv("ssb200 step (scan + algebra, one CTA per signal)"); launch_step(threads, nch, gs, (unsigned)known, smem, st, a, kb, ks); }
             L.end(sp_step);
             L.counters[0]++;
             route.push_back(5);
@@ -578,6 +568,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     a.tol = tol; a.max_iter = max_iter; a.cnt = cnt;
     void* params[] = { &a };
     const int span = L.begin(timing, 1);
+    nvtx_range nv("ssb200 single-signal solve");
     SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS>, dim3((unsigned)grid), dim3(THREADS), params, smem, st));
     L.end(span);
     L.counters[0]++;
@@ -622,15 +613,16 @@ void Homotopy<T>::solve_batch_dev(const T* dY, size_t batch, size_t ldy, T tol, 
 
 template <typename T>
 void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, uint32_t max_iter, T* X, size_t ldx,
-                                   uint32_t* iters, double* errs)
+                                   uint32_t* iters, double* errs, const SparseOut* sp)
 {
     SSB_REQUIRE(M > 0, "no dictionary");
     SSB_REQUIRE(max_iter > 0, "max_iterations must be positive");
     if (batch == 0) return;
-    SSB_REQUIRE(ldy >= (size_t)M && ldx >= (size_t)N, "leading dimensions too small");
+    SSB_REQUIRE(ldy >= (size_t)M && (sp || ldx >= (size_t)N), "leading dimensions too small");
     const int kmax = active_set_capacity(max_iter, N);
     check_capacity(kmax);                                   // before anything is queued
-    if (batch == 1 && solve_single(Y, true, tol, max_iter, X, true, iters, errs, true)) return;
+    SSB_REQUIRE(!sp || (sp->idx && sp->val && sp->count && sp->cap >= (size_t)kmax), "sparse result: cap must be at least min(max_iterations + 1, N)");
+    if (!sp && batch == 1 && solve_single(Y, true, tol, max_iter, X, true, iters, errs, true)) return;
     size_t cap; int nlanes;
     plan_batch(batch, kmax, true, cap, nlanes);
 
@@ -664,6 +656,8 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
     // threads under the first pieces' kernels.  The caller sees the same dense X.
     bool sparse_out = batch >= 4096 && (size_t)N >= 8 * (size_t)kmax;
     if (const char* e = getenv("SSB200_HOST_SPARSE")) sparse_out = sparse_out && atoi(e) != 0;             // tuning knob
+    if (sp) sparse_out = true;                               // the caller takes the sparse form itself: no dense rows at all
+    const bool dense_rows = !sp;
     std::vector<std::thread> zero_threads;
     std::mutex zero_mu;
     bool zero_joined = false;
@@ -671,11 +665,19 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         std::lock_guard<std::mutex> g(zero_mu);
         if (!zero_joined) { for (auto& t : zero_threads) t.join(); zero_joined = true; }
     };
-    if (sparse_out) {
-        // helper threads: half the host cores, shared between the GPUs of the box (one process per GPU each runs this), 2..8
+    if (sparse_out && dense_rows) {
+        // helper threads: half the cores this process may run on (its affinity mask: ranks pinned to disjoint core sets each
+        // size their own pool), else the box's cores shared between its GPUs (one process per GPU each runs this); 2..8
         int ngpu = 1;
         if (cudaGetDeviceCount(&ngpu) != cudaSuccess || ngpu < 1) { ngpu = 1; cudaGetLastError(); }
-        int nz = (int)std::max(2u, std::min(8u, std::thread::hardware_concurrency() / (2u * (unsigned)ngpu)));
+        unsigned cores = std::thread::hardware_concurrency();
+        bool pinned = false;
+        cpu_set_t set;
+        if (sched_getaffinity(0, sizeof(set), &set) == 0) {
+            const unsigned mine = (unsigned)CPU_COUNT(&set);
+            if (mine > 0 && mine < cores) { cores = mine; pinned = true; }
+        }
+        int nz = (int)std::max(2u, std::min(8u, cores / (2u * (pinned ? 1u : (unsigned)ngpu))));
         if (const char* e = getenv("SSB200_ZERO_THREADS")) nz = std::max(1, std::min(64, atoi(e)));      // tuning knob
         const size_t per = (batch + nz - 1) / nz;
         for (int t = 0; t < nz; ++t) {
@@ -708,9 +710,8 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
             L.stIt[i].reserve(big * sizeof(uint32_t));
             L.stErr[i].reserve(big * sizeof(double));
             if (sparse_out) {
-                L.stIdx[i].reserve(big * kmax * sizeof(int)); L.hIdx[i].reserve(big * kmax * sizeof(int));
-                L.stVal[i].reserve(big * kmax * sizeof(T));   L.hVal[i].reserve(big * kmax * sizeof(T));
-                L.stCnt[i].reserve(big * sizeof(int));        L.hCnt[i].reserve(big * sizeof(int));
+                L.stIdx[i].reserve(big * kmax * sizeof(int)); L.stVal[i].reserve(big * kmax * sizeof(T)); L.stCnt[i].reserve(big * sizeof(int));
+                if (dense_rows) { L.hIdx[i].reserve(big * kmax * sizeof(int)); L.hVal[i].reserve(big * kmax * sizeof(T)); L.hCnt[i].reserve(big * sizeof(int)); }
             }
         }
         L.toggle = 0;
@@ -731,11 +732,22 @@ void Homotopy<T>::solve_batch_host(const T* Y, size_t batch, size_t ldy, T tol, 
         if (nocopy) return;
         if (sparse_out) {
             int* d_idx = L.stIdx[b].template as<int>(); T* d_val = L.stVal[b].template as<T>(); int* d_cnt = L.stCnt[b].template as<int>();
-            int* h_idx = L.hIdx[b].template as<int>();  T* h_val = L.hVal[b].template as<T>();  int* h_cnt = L.hCnt[b].template as<int>();
             compress_rows_kernel<T><<<(unsigned)((rows + 3) / 4), 128, 0, L.copy_out>>>(L.stX[b].template as<T>(), (size_t)N, N, rows, kmax,
                                                                                       d_idx, d_val, d_cnt);
             SSB_CUDA(cudaGetLastError());
             L.counters[0]++;
+            if (!dense_rows) {   // straight into the caller's arrays (row stride cap >= kmax): nothing to zero, nothing to scatter
+                SSB_CUDA(cudaMemcpyAsync(sp->count + b0, d_cnt, rows * sizeof(int), cudaMemcpyDeviceToHost, L.copy_out));
+                SSB_CUDA(cudaMemcpy2DAsync(sp->idx + b0 * sp->cap, sp->cap * sizeof(int), d_idx, kmax * sizeof(int), kmax * sizeof(int), rows,
+                                           cudaMemcpyDeviceToHost, L.copy_out));
+                SSB_CUDA(cudaMemcpy2DAsync(sp->val + b0 * sp->cap, sp->cap * sizeof(T), d_val, kmax * sizeof(T), kmax * sizeof(T), rows,
+                                           cudaMemcpyDeviceToHost, L.copy_out));
+                SSB_CUDA(cudaMemcpyAsync(iters + b0, L.stIt[b].p, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.copy_out));
+                SSB_CUDA(cudaMemcpyAsync(errs + b0, L.stErr[b].p, rows * sizeof(double), cudaMemcpyDeviceToHost, L.copy_out));
+                SSB_CUDA(cudaEventRecord(L.ev_out[b], L.copy_out));
+                return;
+            }
+            int* h_idx = L.hIdx[b].template as<int>();  T* h_val = L.hVal[b].template as<T>();  int* h_cnt = L.hCnt[b].template as<int>();
             SSB_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, rows * sizeof(int), cudaMemcpyDeviceToHost, L.copy_out));
             SSB_CUDA(cudaMemcpyAsync(h_idx, d_idx, rows * kmax * sizeof(int), cudaMemcpyDeviceToHost, L.copy_out));
             SSB_CUDA(cudaMemcpyAsync(h_val, d_val, rows * kmax * sizeof(T), cudaMemcpyDeviceToHost, L.copy_out));
@@ -774,7 +786,7 @@ double Homotopy<T>::debug_contract(const T* P, size_t rows, T* Q, int path, int 
     SSB_REQUIRE(M > 0 && rows > 0 && reps > 0, "bad arguments");
     Lane& L = lane(0);
     reserve_workspace(L, rows, 2);
-    const bool tc = path >= 2;
+    const bool tc = path == 2 || path == 3;
     SSB_REQUIRE(!tc || (sizeof(T) == 4 && tc_supported(Npad, Mp)), "tcgen05 contraction unavailable for this dtype/shape");
     struct restore { int& ref; int v; ~restore() { ref = v; } } guard{ contraction_path, contraction_path };
     contraction_path = path;                                 // 2: fp16 containers, 3: tf32 containers

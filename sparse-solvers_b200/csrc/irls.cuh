@@ -105,9 +105,6 @@ public:
         Rc_.reserve(rc.size() * sizeof(T));
         SSB_CUDA(cudaMemcpyAsync(Qt_.p, qt.data(), qt.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
         SSB_CUDA(cudaMemcpyAsync(Rc_.p, rc.data(), rc.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
-        // E = Q^T Q with its rounding-level off-diagonals
-        E_.reserve((size_t)Npad * Npad * sizeof(T));
-        counters[0] += launch_contract_simt<T>(Qt_.as<T>(), Mp, Npad, Mp, Qt_.as<T>(), Mp, Npad, E_.as<T>(), Npad, stream);
         SSB_CUDA(cudaStreamSynchronize(stream));
     }
 
@@ -158,7 +155,7 @@ public:
             end_span(span, st);
             counters[1]++; counters[2] += rows;
             IrlsArgs<T> a{};
-            a.N = N; a.lde = Npad; a.E = E_.as<T>(); a.Qt = Qt_.as<T>(); a.M = M; a.ldq = Mp; a.Rc = Rc_.as<T>(); a.S = S_.as<T>();
+            a.N = N; a.lde = Npad; a.Tq = P_.as<T>(); a.Qt = Qt_.as<T>(); a.M = M; a.ldq = Mp; a.Rc = Rc_.as<T>(); a.S = S_.as<T>();
             a.X = dX + b0 * ldx; a.ldx = ldx; a.L = L_.as<T>(); a.vec = vec_.as<T>();
             a.iters = d_iters + b0; a.errs = d_errs + b0; a.spd = d_spd + b0;
             a.tol = tol; a.max_iter = max_iter;
@@ -194,7 +191,7 @@ public:
     }
 
 private:
-    dev_buffer Qt_, Rc_, E_, L_, vec_, S_, P_;
+    dev_buffer Qt_, Rc_, L_, vec_, S_, P_;
     size_t planned_batch_ = 0, planned_chunk_ = 0;
 };
 

@@ -5,7 +5,10 @@
 //
 // With A = QR (thin, M >= N) the reference forms, every iteration,
 //     G = Q^T (Q o w),  L = chol(tril(G)),  s = L^-T L^-1 (Q^T y),  x = R^-1 Q^T (Q s).
-// Q^T y comes from one batched contraction and Q^T (Q s) = E s with E = Q^T Q computed once.
+// Q^T y comes from one batched contraction; t = Q s and x = Q^T t are formed as the reference forms them (two products with
+// Q, irls-cpu.cpp:55-57).  Replacing them by E s with a precomputed E = Q^T Q is the same algebra, but once the iterates blow
+// up (at the C4 shape they pass 1e23 by the fifth iteration and the solve ends when a weight drops under eps^2) what is
+// amplified is the rounding structure of exactly these products, and the shortcut ended one solve in four an iteration late.
 // G is formed the reference's way -- column j of Q scaled by w_j first, then the dot products over
 // the M rows in order, multiply and add rounded separately -- because the way most solves END depends
 // on it: the last pivots are w_j minus rounding-level terms, and whether sqrt(pivot) comes out
@@ -21,7 +24,7 @@ template <typename T>
 struct IrlsArgs {
     int N;              // columns of A
     int lde;            // leading dimension of E and S (= Npad)
-    const T* E;         // [N][lde]   Q^T Q
+    T* Tq;              // [rows][ldq] scratch: t = Q s (the staged signal row, free once Q^T y is formed)
     const T* Qt;        // [Npad][ldq] columns of Q, contiguous
     int M, ldq;
     const T* Rc;        // [N][N]     R stored column-major: Rc[i*N + k] = R[k][i]
@@ -194,10 +197,17 @@ __global__ void __launch_bounds__(THREADS) irls_solve_kernel(IrlsArgs<T> a)
             if (tid == 0) sv[i] = (sv[i] - acc) / L[(size_t)i * N + i];
             __syncthreads();
         }
-        // xnext = Q^T (Q s) = E s  (:55-57)
+        // t = Q s (:55), xnext = Q^T t (:57)
+        T* tq = a.Tq + b * (size_t)a.ldq;
+        for (int m = tid; m < a.ldq; m += THREADS) {       // column j of Q is row j of Qt: coalesced over m, j in order
+            T acc = T(0);
+            for (int j = 0; j < N; ++j) acc += a.Qt[(size_t)j * a.ldq + m] * sv[j];
+            tq[m] = acc;
+        }
+        __syncthreads();
         for (int r = warp; r < N; r += NW) {
             T acc = T(0);
-            for (int k = lane; k < N; k += 32) acc += a.E[(size_t)r * a.lde + k] * sv[k];
+            for (int m = lane; m < a.M; m += 32) acc += a.Qt[(size_t)r * a.ldq + m] * tq[m];
             acc = warp_sum(acc);
             if (lane == 0) xn[r] = acc;
         }

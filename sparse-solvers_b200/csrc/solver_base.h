@@ -29,7 +29,8 @@ struct SolverBase {
     uint64_t kernel_rows[NCLS] = { 0, 0, 0, 0, 0, 0 };
     uint64_t kernel_bytes[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // algorithmic HBM bytes of those launches (classes 2-5); [6] = L2 bytes of the Gram rows
     std::atomic<uint64_t> h2d_bytes{ 0 }, d2h_bytes{ 0 };   // bytes the host-pointer batch entries moved over PCIe since the last reset
-    int contraction_path = 0;            // 0 auto, 1 SIMT, 2 tcgen05 (fp16 containers), 3 tcgen05 with tf32 containers
+    int contraction_path = 0;            // 0 auto, 1 no tcgen05 (float32: FFMA tiles; float64: DMMA), 2 tcgen05 (fp16 containers),
+                                         // 3 tcgen05 with tf32 containers, 4 plain FFMA / DFMA tiles (the checker of the tensor kernels)
 
     // pairs of events bracketing launches of class `cls` on the current solve's stream
     struct span { cudaEvent_t a, b; int cls; };

@@ -15,7 +15,7 @@ import numpy as np
 from ._lib import SolverError, check, lib
 
 __all__ = ["Homotopy", "HomotopyGroup", "Irls", "HomotopyReport", "IrlsReport", "version", "SolverError",
-           "reconstruct_signal", "norm_l1"]
+           "reconstruct_signal", "norm_l1", "fp64_peak"]
 
 
 def version():
@@ -167,7 +167,7 @@ class _Solver:
         return int(b[0]), int(b[1])
 
     def set_contraction_path(self, path):
-        check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path])))
+        check(lib().ssb200_set_contraction_path(self._h, C.c_int({"auto": 0, "simt": 1, "tcgen05": 2, "tcgen05-tf32": 3, "fma": 4}[path])))
 
 
 class Homotopy(_Solver):
@@ -186,19 +186,33 @@ class Homotopy(_Solver):
     def solve_batch(self, Y, tolerance=None, max_iterations=100, out=None, sparse=False):
         """Y: (B, M) rows are signals.  Returns X (B, N), iters (B,) uint32, solution_errors (B,) float64.
 
+        sparse=True (host arrays too): the coefficients come back as (indices (B, cap) int32, values (B, cap), counts (B,) int32),
+        cap = min(max_iterations + 1, N), entries beyond counts[b] unspecified -- no dense rows are formed anywhere.
+
         Y may also live on the device (torch CUDA tensor, or any DLPack / __cuda_array_interface__ producer): nothing is
         copied through the host, the work is queued on torch's current stream and X, iters (int32), solution_errors come
         back as torch tensors on that device.  With sparse=True the coefficients come back as (indices (B, cap) int32,
         values (B, cap), counts (B,) int32) with cap = min(max_iterations + 1, N) instead of the dense X."""
         if _is_cuda(Y):
             return self._solve_batch_cuda(_as_torch(Y), tolerance, max_iterations, out, sparse)
-        if sparse:
-            raise ValueError("sparse=True is for device-resident signals; compress host results with numpy")
         self._check_signal(Y, 2)
         if Y.strides[1] != Y.itemsize:
             Y = np.ascontiguousarray(Y)
         tol, mi = self._defaults(tolerance, max_iterations)
         B = Y.shape[0]
+        if sparse:
+            if out is not None:
+                raise ValueError("out= is for the dense result")
+            cap = max(1, min(int(max_iterations) + 1, self.shape[1]))
+            idx = np.empty((B, cap), dtype=np.int32)
+            val = np.empty((B, cap), dtype=self.dtype)
+            cnt = np.empty(B, dtype=np.int32)
+            iters = np.empty(B, dtype=np.uint32)
+            errs = np.empty(B, dtype=np.float64)
+            check(getattr(lib(), f"ssb200_homotopy_solve_batch_sparse_{self._sfx}")(
+                self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize if B > 1 else self.shape[0]), tol, mi,
+                _ptr(idx), _ptr(val), _ptr(cnt), C.c_size_t(cap), _ptr(iters), _ptr(errs)))
+            return (idx, val, cnt), iters, errs
         X = out if out is not None else np.empty((B, self.shape[1]), dtype=self.dtype)
         if out is not None:      # the C side writes B rows of N values through this pointer: everything it assumes is checked here
             if not isinstance(X, np.ndarray) or X.dtype != self.dtype or X.shape != (B, self.shape[1]):
@@ -210,7 +224,7 @@ class Homotopy(_Solver):
         iters = np.empty(B, dtype=np.uint32)
         errs = np.empty(B, dtype=np.float64)
         fn = getattr(lib(), f"ssb200_homotopy_solve_batch_{self._sfx}")
-        check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
+        check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize if B > 1 else self.shape[0]), tol, mi,
                  _ptr(X), C.c_size_t(X.strides[0] // X.itemsize if B > 1 else self.shape[1]), _ptr(iters), _ptr(errs)))
         return X, iters, errs
 
@@ -272,7 +286,7 @@ class Homotopy(_Solver):
         Q = np.empty((P.shape[0], self.shape[1]), dtype=self.dtype)
         ms = C.c_double()
         check(getattr(lib(), f"ssb200_debug_contract_{self._sfx}")(
-            self._h, _ptr(P), C.c_size_t(P.shape[0]), _ptr(Q), C.c_int({"simt": 1, "tcgen05": 2, "tcgen05-tf32": 3}[path]), C.c_int(reps),
+            self._h, _ptr(P), C.c_size_t(P.shape[0]), _ptr(Q), C.c_int({"simt": 1, "tcgen05": 2, "tcgen05-tf32": 3, "fma": 4}[path]), C.c_int(reps),
             C.byref(ms)))
         return Q, ms.value
 
@@ -404,6 +418,13 @@ class Irls(_Solver):
         check(fn(self._h, _ptr(Y), C.c_size_t(B), C.c_size_t(Y.strides[0] // Y.itemsize), tol, mi,
                  _ptr(X), C.c_size_t(X.shape[1]), _ptr(iters), _ptr(errs), _ptr(spd)))
         return X, iters, errs, spd.astype(bool)
+
+
+def fp64_peak(kind="dmma", device=0):
+    """Measured FP64 peak of the device in TFLOP/s: independent DFMA chains ("dfma") or mma.sync.m8n8k4.f64 tiles ("dmma")."""
+    t = C.c_double()
+    check(lib().ssb200_fp64_peak_probe(C.c_int(device), C.c_int({"dfma": 0, "dmma": 1}[kind]), C.byref(t)))
+    return t.value
 
 
 def reconstruct_signal(A, x, device=0):

@@ -95,7 +95,7 @@ def test_float64_and_argument_checks(case):
     with pytest.raises(ValueError):
         s.solve_batch(torch.zeros((4, 100), dtype=torch.float32, device="cuda"), 1e-3, 40)
     with pytest.raises(ValueError):
-        s.solve_batch(Y, 1e-3, 40, sparse=True)
+        s.solve_batch(Y, 1e-3, 40, sparse=True, out=np.zeros((200, 512), dtype=np.float32))   # out= belongs to the dense form
     with pytest.raises(TypeError):
         ss.Irls(torch.from_numpy(A.T.copy()).cuda())
     X0, it0, e0 = s.solve_batch(torch.zeros((0, 128), dtype=torch.float32, device="cuda"), 1e-3, 40)
@@ -121,3 +121,24 @@ def test_host_entry_sparse_return_equals_device_entry(pad):
     assert (it == dit.cpu().numpy().astype(np.uint32)).all() and np.array_equal(err, derr.cpu().numpy())
     if pad:
         assert (wide[:, 1024:] == np.float32(3.5)).all()       # columns outside the view are not touched
+
+
+@pytest.mark.parametrize("batch", [3, 200, 8192 + 77])
+def test_host_entry_sparse_result(batch):
+    """ssb200_homotopy_solve_batch_sparse_*: the host-pointer entry hands the coefficients back as (index, value) x cap + count per
+    signal -- no dense row is formed on the host; scattered back they are the dense result, entry for entry."""
+    import sparsesolvers as ss
+    from sparsesolvers import synth
+    A = synth.dictionary(128, 1024, dtype=np.float32, seed=41)
+    Y, _ = synth.sparse_signals(A, batch, 8, seed=42)
+    s = ss.Homotopy(A)
+    X, it, err = s.solve_batch(Y, 1e-3, 40)
+    (idx, val, cnt), its, errs = s.solve_batch(Y, 1e-3, 40, sparse=True)
+    assert idx.shape == (batch, 41) and (its == it).all() and np.array_equal(errs, err)
+    assert (cnt == (X != 0).sum(axis=1)).all()
+    dense = np.zeros_like(X)
+    for b in range(batch):
+        k = cnt[b]
+        assert (np.diff(idx[b, :k]) > 0).all()
+        dense[b, idx[b, :k]] = val[b, :k]
+    assert np.array_equal(dense, X)
