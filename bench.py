@@ -329,13 +329,14 @@ def run_grid(args, cfg):
                     it_ref[i] = itr[0]
                     hay[::2, n] -= 1.0
                     done += 1
-                    if time.perf_counter() - t0 > 8.0:
+                    if time.perf_counter() - t0 > 12.0:
                         break
                 cpu_s = time.perf_counter() - t0
                 cell.update(cpu_ms_per_solve=1e3 * cpu_s / done, cpu_solves=done, cpu_mean_iters=float(it_ref[:done].mean()),
                             gpu_mean_iters_same_solves=float(it_gpu[:done].mean()),
                             iters_equal=int((it_ref[:done] == it_gpu[:done]).sum()),
-                            gpu_hit_max_iter=int((it_gpu == N).sum()), cpu_hit_max_iter=int((it_ref[:done] == N).sum()))
+                            gpu_hit_max_iter=int((it_gpu[:done] == N).sum()), cpu_hit_max_iter=int((it_ref[:done] == N).sum()),
+                            gpu_hit_max_iter_all_solves=int((it_gpu == N).sum()))
             cells.append(cell)
             total_gpu += gpu_s
             total_n += solves

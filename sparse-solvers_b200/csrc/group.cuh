@@ -5,8 +5,10 @@
 //   host-pointer entry    every GPU's thread copies its shard in and out itself: the "gather" is the caller's X array
 //   device-pointer entry  Y, X and the reports live on the group's first GPU: shards travel over NVLink with
 //                         ncclSend / ncclRecv, the dense coefficient rows come back the same way
-// NCCL is bound at run time (dlopen of libnccl.so.2: the copy torch already loaded, or the system one), so libssb200.so has
-// no link-time dependency on it and single-GPU users never touch it.
+// NCCL is bound at run time (dlopen of libnccl.so.2: the copy the process already loaded -- e.g. torch's --, else
+// $SSB200_NCCL_LIB, else the system one), so libssb200.so has no link-time dependency on it and single-GPU users never touch
+// it.  A Python process that will import torch later should load torch's copy first (sparsesolvers.HomotopyGroup does): two
+// NCCL versions share one soname, and whichever is loaded first is the one every later DT_NEEDED resolves to.
 #pragma once
 
 #include <dlfcn.h>
@@ -35,9 +37,13 @@ struct NcclApi {
         static NcclApi api;
         static std::once_flag once;
         std::call_once(once, [] {
+            // the copy the process already has (torch's bundled one, when torch came first) > $SSB200_NCCL_LIB > the system one.
+            // Never RTLD_GLOBAL: a second NCCL of another version must not shadow the symbols of the first.
+            api.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+            if (!api.lib) if (const char* e = getenv("SSB200_NCCL_LIB")) api.lib = dlopen(e, RTLD_NOW | RTLD_LOCAL);
             for (const char* name : { "libnccl.so.2", "libnccl.so" }) {
-                api.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
                 if (api.lib) break;
+                api.lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
             }
             if (!api.lib) return;
             auto sym = [&](const char* n) { return dlsym(api.lib, n); };

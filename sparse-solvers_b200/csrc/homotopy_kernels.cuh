@@ -232,7 +232,27 @@ __device__ __forceinline__ void write_rhs(const HomArgs<T>& a, int row, int sig,
         T acc[V], accr[V];
 #pragma unroll
         for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
-        for (int k = 0; k < K; ++k) {
+        // eight atoms per round: their rows are fetched together (eight independent 16-byte loads in flight per thread -- with
+        // one CTA per signal and K of them in a row this loop is L2 latency, not bandwidth), then added in k order
+        int k = 0;
+        for (; k + 8 <= K; k += 8) {
+            T av[8][V];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                *reinterpret_cast<int4*>(av[u]) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k + u] * a.Mp + m0));
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const T dk = s_d[k + u];
+#pragma unroll
+                for (int e = 0; e < V; ++e) acc[e] += av[u][e] * dk;
+                if (res) {
+                    const T xk = s_x[k + u];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) accr[e] += av[u][e] * xk;
+                }
+            }
+        }
+        for (; k < K; ++k) {
             T av[V];
             *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
             const T dk = s_d[k];

@@ -329,7 +329,20 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     T acc[V], accr[V];
 #pragma unroll
                     for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
-                    for (int k = 0; k < Knew; ++k) {
+                    int k = 0;
+                    for (; k + 8 <= Knew; k += 8) {   // eight rows in flight per thread: this loop is L2 latency on ONE CTA
+                        T av8[8][V];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            *reinterpret_cast<int4*>(av8[u]) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k + u] * a.Mp + m0));
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const T dk = s_d[k + u], xk = s_x[k + u];
+#pragma unroll
+                            for (int e = 0; e < V; ++e) { acc[e] += av8[u][e] * dk; accr[e] += av8[u][e] * xk; }
+                        }
+                    }
+                    for (; k < Knew; ++k) {
                         T av[V];
                         *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
                         const T dk = s_d[k], xk = s_x[k];

@@ -327,12 +327,29 @@ class HomotopyGroup:
     broadcast, solve_batch cuts the batch into contiguous shards, one host thread per GPU; results come back in the caller's
     arrays.  New functionality (the reference solves one signal per call on the CPU, include/ss/ss.h:50)."""
 
+    @staticmethod
+    def _preload_nccl():
+        """The library binds NCCL at run time by soname.  torch ships its own (newer) libnccl.so.2: if the system copy were loaded
+        first, a later `import torch` would resolve to it and fail on missing symbols -- so torch's copy, when installed, goes first."""
+        import importlib.util
+        import os
+        try:
+            spec = importlib.util.find_spec("nvidia.nccl")
+            for d in (spec.submodule_search_locations if spec else []):
+                p = os.path.join(d, "lib", "libnccl.so.2")
+                if os.path.exists(p):
+                    C.CDLL(p, mode=C.RTLD_GLOBAL)
+                    return
+        except (ImportError, OSError, ValueError):
+            pass
+
     def __init__(self, A, devices=None):
         A = np.asarray(A)
         if A.ndim != 2:
             raise ValueError("A must be 2-dimensional")
         if A.dtype not in _SFX:
             raise TypeError("A must be float32 or float64")
+        self._preload_nccl()
         if devices is None:
             devices = list(range(max(1, lib().ssb200_device_count())))
         self.devices = [int(d) for d in devices]
