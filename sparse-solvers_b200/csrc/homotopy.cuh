@@ -236,6 +236,7 @@ private:
         std::vector<cudaEvent_t> pool;
         std::vector<cudaEvent_t> count_events, iter_events;   // one pair per iteration in flight (count read-back)
         cudaStream_t side = nullptr;                          // the read-backs' own stream
+        dev_buffer fin_ws;                                    // the finisher's scratch
         Lane() { SSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
         ~Lane() {
             drop_plans();
@@ -344,6 +345,11 @@ private:
     void solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T tol, uint32_t max_iter, T* dX, size_t ldx,
                      uint32_t* d_iters, double* d_errs);
     void merge(Lane& L);
+    // the finisher: the last <= FIN_MAX signals of a chunk taken from their lockstep state to the end by the cooperative
+    // single-signal kernel in resume mode (homotopy_single.cuh); false = shape not supported, the lockstep loop goes on
+    static constexpr int FIN_MAX = 4, FIN_AFTER = 6;
+    bool launch_finisher(Lane& L, const HomArgs<T>& a, uint32_t it0, const int* d_act, const int* d_count);
+    std::mutex coop_mu_;                 // one cooperative grid at a time per handle (two lanes must not wait on each other's CTAs)
     // one signal: the whole solve in one cooperative kernel (homotopy_single.cuh); false = shape not supported
     bool solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters, double* errs,
                       bool reports_on_host);

@@ -375,6 +375,8 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     size_t known = rows;         // newest count the host has seen (upper bound of the current one)
     uint32_t seen = 0;           // ... which is the count of iteration `seen`
     uint32_t last = 0;
+    uint32_t thin_run = 0;       // consecutive iterations entered with at most a thin tile's worth of signals
+    bool finished_by_kernel = false;
     std::vector<int> hist{ (int)rows };                    // hist[j] = signals that continue after iteration j
     std::vector<uint8_t> route{ 0 };                        // launch class of every iteration's scan (kernel profile)
     // debugging aid (SSB200_TRACE_STALL=<ms>): host timeline of a chunk that took longer than <ms> -- when each iteration was
@@ -398,6 +400,16 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
         }
         const double t_wait = trace_ms > 0 ? now_ms() : 0.0;
         if (known == 0) break;
+        // Stragglers: once the chunk has been down to a thin tile's worth of signals for FIN_AFTER iterations (the bulk converges
+        // within four or five iterations of each other, so these go on to max_iterations) and no more than FIN_MAX are left,
+        // they are handed to the finisher.  Only such signals ever see it, so a converging signal's arithmetic does not depend
+        // on the batch it travels in.
+        thin_run = known <= 32 ? thin_run + 1 : 0;
+        if (known <= (size_t)FIN_MAX && thin_run > (uint32_t)FIN_AFTER && it > 1 && rows > 1 &&
+            launch_finisher(L, a, it - 1, L.act[cur].template as<int>(), d_counts + slot(it - 1))) {
+            finished_by_kernel = true;
+            break;
+        }
         last = it;
         const bool gram = it < gram_iters;
         a.skip_rhs = (it + 1 < gram_iters) ? 1 : 0;
@@ -457,6 +469,7 @@ void Homotopy<T>::solve_chunk(Lane& L, const T* dY, size_t rows, size_t ldy, T t
     SSB_CUDA(cudaStreamSynchronize(st));
     SSB_CUDA(cudaStreamSynchronize(L.side));
     for (uint32_t j = seen + 1; j <= last; ++j) hist.push_back(h_ring[slot(j)]);   // at most RUN_AHEAD + 1 unread slots, none reused yet
+    (void)finished_by_kernel;
     if (trace_ms > 0 && now_ms() > trace_ms) {
         fprintf(stderr, "[ssb200] slow chunk: %.2f ms (loop queued by %.2f ms, %zu rows)\n", now_ms(), t_loop, rows);
         for (size_t i = 0; i < trace.size(); ++i)
@@ -527,6 +540,49 @@ void Homotopy<T>::run_lanes(int nlanes, size_t nchunks, F&& body)
     for (int li = 0; li < nlanes; ++li) if (err[li]) std::rethrow_exception(err[li]);
 }
 
+
+template <typename T>
+bool Homotopy<T>::launch_finisher(Lane& L, const HomArgs<T>& h, uint32_t it0, const int* d_act, const int* d_count)
+{
+    if (const char* e = getenv("SSB200_FINISHER")) if (atoi(e) == 0) return false;                     // tuning knob
+    constexpr int THREADS = 256;
+    int sms = 0, coop = 0;
+    SSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    SSB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+    if (!coop) return false;
+    const int kmax = L.ws_kmax;
+    const int ks = (kmax + 1) | 1;
+    const int grid = std::min(sms, (Npad + 7) / 8);
+    const int cnt = (Npad + grid - 1) / grid;
+    const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
+    if (smem > 200 * 1024) return false;
+    static std::atomic<uint64_t> configured{ 0 };
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS>, configured);
+    // scratch: P | R | Cg | part_t | part_max | part_i
+    const size_t nT = (size_t)2 * Mp + Npad + 2 * (size_t)grid + 8;
+    L.fin_ws.reserve(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64);
+    T* w = L.fin_ws.template as<T>();
+    SingleArgs<T> a{};
+    a.N = N; a.Npad = Npad; a.Mp = Mp; a.Kmax = kmax; a.ks = ks;
+    a.At = At_; a.G = G_; a.ldg = Npad;
+    a.P = w; a.R = w + Mp; a.Cg = a.R + Mp; a.part_t = a.Cg + Npad; a.part_max = a.part_t + grid;
+    a.part_i = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(w) + round_up((size_t)(a.part_max + grid - w) * sizeof(T), 16));
+    a.exact = h.exact; a.tol = h.tol; a.max_iter = h.max_iter; a.cnt = cnt;
+    a.resume = 1; a.act = d_act; a.count = d_count; a.max_sigs = FIN_MAX; a.it0 = it0;
+    a.Y = h.Y; a.ldy = h.ldy; a.M = h.M; a.X = h.X; a.ldx = h.ldx; a.C = h.C; a.ldc = h.ldc;
+    a.gamv = h.gam; a.dGv = h.dG; a.Ginvv = h.Ginv; a.lamv = h.lam; a.Kcurv = h.Kcur; a.Kstate = h.Kmax;
+    a.itersv = h.iters; a.errsv = h.errs;
+    void* params[] = { &a };
+    nvtx_range nv("ssb200 finisher (stragglers to the end)");
+    // a cooperative grid needs every SM: two lanes launching one each could each hold half the machine and wait forever
+    std::lock_guard<std::mutex> g(coop_mu_);
+    const int span = L.begin(timing, 5);
+    SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS>, dim3((unsigned)grid), dim3(THREADS), params, smem, L.stream));
+    L.end(span);
+    L.counters[0]++;
+    SSB_CUDA(cudaStreamSynchronize(L.stream));
+    return true;
+}
 
 template <typename T>
 bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters,

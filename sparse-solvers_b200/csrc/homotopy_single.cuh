@@ -33,6 +33,19 @@ struct SingleArgs {
     uint32_t* iters; double* errs;
     T tol; uint32_t max_iter;
     int cnt;              // atoms per CTA
+    // ---- resume mode: the finisher of the lockstep loop.  The last few still-running signals of a chunk (stragglers that go on
+    // to max_iterations long after the rest has converged) are taken from their lockstep state to the end here, one after the
+    // other: an iteration then costs grid barriers instead of two thin launches and a host round trip.
+    int resume;            // 0: one signal from scratch (y, x); 1: signals act[0 .. min(*count, max_sigs)) from their state
+    const int* act;        // position -> signal (nullptr: identity)
+    const int* count;
+    int max_sigs;
+    uint32_t it0;          // iterations the lockstep loop has completed
+    const T* Y; size_t ldy; int M;       // the signals, caller layout (exact mode: r = y - A_G x_G)
+    T* X; size_t ldx;      // coefficient rows
+    const T* C; int ldc;   // correlations by signal (incremental mode)
+    const uint32_t* gamv; const T* dGv; const T* Ginvv; const T* lamv; const int* Kcurv; int Kstate;   // lockstep state, Kstate slots per signal
+    uint32_t* itersv; double* errsv;     // reports, by signal
 };
 
 template <typename T>
@@ -115,65 +128,127 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         __syncthreads();
     };
 
-    // ---- initial state (homotopy-cpu.cpp:201-229)
-    for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = a.y[m];
-    for (int n = a0 + tid; n < a1; n += THREADS) { s_act[n - a0] = 0u; if (n < a.N) a.x[n] = T(0); }
-    __syncthreads();
-    correlate(s_p);
-    __syncthreads();
-    {
-        T best = T(-1);
-        uint32_t bidx = 0xffffffffu;
-        for (int n = a0 + tid; n < a1; n += THREADS) {
-            s_c[n - a0] = s_q[n - a0];
-            if (n < a.N) { const T av = fabs(s_q[n - a0]); if (av > best) { best = av; bidx = (uint32_t)n; } }
-        }
-        warp_argmax_first(best, bidx);
-        if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
-        __syncthreads();
-        if (tid == 0) {
-            for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
-            a.part_t[cta] = best; a.part_i[cta] = bidx;
-            if (cta == 0) a.part_max[0] = fabs(s_q[0]);
-        }
-    }
-    grid.sync();
-    T lam;
+    const int nsig = a.resume ? min(*a.count, a.max_sigs) : 1;
+    for (int si = 0; si < nsig; ++si) {
+    const int s = a.resume ? (a.act ? a.act[si] : si) : 0;
+    T* xrow = a.resume ? a.X + (size_t)s * a.ldx : a.x;
+    const T* yrow = a.resume ? a.Y + (size_t)s * a.ldy : a.y;
+    const int ylen = a.resume ? a.M : a.Mp;          // a.y is zero padded to Mp, a caller's row is not
+    uint32_t* it_out = a.resume ? a.itersv + s : a.iters;
+    double* err_out = a.resume ? a.errsv + s : a.errs;
+    uint32_t it = 0;
+    T lam = T(0);
     int K = 1;
-    {
-        T best = T(-1);
-        uint32_t bidx = 0xffffffffu;
-        for (int g = tid; g < G; g += THREADS) {
-            const T v = a.part_t[g]; const uint32_t i = a.part_i[g];
-            if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
-        }
-        warp_argmax_first(best, bidx);
-        if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+    // p = A_G d (:112-116), k ascending per element as write_rhs; exact mode: r = y - A_G x_G (:94-96); CTA 0 only
+    auto publish_rhs = [&](int Knew) {
+                for (int m0 = tid * V; m0 < a.Mp; m0 += THREADS * V) {
+                    T acc[V], accr[V];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
+                    int k = 0;
+                    for (; k + 8 <= Knew; k += 8) {   // eight rows in flight per thread: this loop is L2 latency on ONE CTA
+                        T av8[8][V];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            *reinterpret_cast<int4*>(av8[u]) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k + u] * a.Mp + m0));
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const T dk = s_d[k + u], xk = s_x[k + u];
+#pragma unroll
+                            for (int e = 0; e < V; ++e) { acc[e] += av8[u][e] * dk; accr[e] += av8[u][e] * xk; }
+                        }
+                    }
+                    for (; k < Knew; ++k) {
+                        T av[V];
+                        *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
+                        const T dk = s_d[k], xk = s_x[k];
+#pragma unroll
+                        for (int e = 0; e < V; ++e) { acc[e] += av[e] * dk; accr[e] += av[e] * xk; }
+                    }
+                    *reinterpret_cast<int4*>(a.P + m0) = *reinterpret_cast<const int4*>(acc);
+                    if (a.exact) {
+#pragma unroll
+                        for (int e = 0; e < V; ++e) accr[e] = (m0 + e < ylen ? yrow[m0 + e] : T(0)) - accr[e];
+                        *reinterpret_cast<int4*>(a.R + m0) = *reinterpret_cast<const int4*>(accr);
+                    }
+                }
+    };
+    if (!a.resume) {
+        // ---- initial state (homotopy-cpu.cpp:201-229)
+        for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = yrow[m];
+        for (int n = a0 + tid; n < a1; n += THREADS) { s_act[n - a0] = 0u; if (n < a.N) xrow[n] = T(0); }
         __syncthreads();
-        best = red_v[0]; bidx = red_i[0];
-        for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
-        if (bidx == 0xffffffffu) { bidx = 0; best = a.part_max[0]; }   // all-NaN correlations
-        lam = best;
-        if ((int)bidx >= a0 && (int)bidx < a1 && tid == 0) s_act[bidx - a0] = 1u;
-        if (cta == 0) {
-            if (tid == 0) {
-                const T nrm = sqrt(a.G[(size_t)bidx * a.ldg + bidx]);       // online_inverse.h:193-201
-                const T inv = T(1) / (nrm * nrm);
-                s_gam[0] = bidx; s_G[0] = inv; s_d[0] = sign_tol(best, a.tol) * inv; s_x[0] = T(0);   // sign of |c|: :223-224
+        correlate(s_p);
+        __syncthreads();
+        {
+            T best = T(-1);
+            uint32_t bidx = 0xffffffffu;
+            for (int n = a0 + tid; n < a1; n += THREADS) {
+                s_c[n - a0] = s_q[n - a0];
+                if (n < a.N) { const T av = fabs(s_q[n - a0]); if (av > best) { best = av; bidx = (uint32_t)n; } }
             }
+            warp_argmax_first(best, bidx);
+            if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
             __syncthreads();
-            const T d0 = s_d[0];
-            for (int m = tid; m < a.Mp; m += THREADS) {
-                a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
-                if (a.exact) a.R[m] = a.y[m];                      // r = y - A 0
+            if (tid == 0) {
+                for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
+                a.part_t[cta] = best; a.part_i[cta] = bidx;
+                if (cta == 0) a.part_max[0] = fabs(s_q[0]);
             }
         }
+        grid.sync();
+        K = 1;
+        {
+            T best = T(-1);
+            uint32_t bidx = 0xffffffffu;
+            for (int g = tid; g < G; g += THREADS) {
+                const T v = a.part_t[g]; const uint32_t i = a.part_i[g];
+                if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
+            }
+            warp_argmax_first(best, bidx);
+            if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
+            __syncthreads();
+            best = red_v[0]; bidx = red_i[0];
+            for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
+            if (bidx == 0xffffffffu) { bidx = 0; best = a.part_max[0]; }   // all-NaN correlations
+            lam = best;
+            if ((int)bidx >= a0 && (int)bidx < a1 && tid == 0) s_act[bidx - a0] = 1u;
+            if (cta == 0) {
+                if (tid == 0) {
+                    const T nrm = sqrt(a.G[(size_t)bidx * a.ldg + bidx]);       // online_inverse.h:193-201
+                    const T inv = T(1) / (nrm * nrm);
+                    s_gam[0] = bidx; s_G[0] = inv; s_d[0] = sign_tol(best, a.tol) * inv; s_x[0] = T(0);   // sign of |c|: :223-224
+                }
+                __syncthreads();
+                const T d0 = s_d[0];
+                for (int m = tid; m < a.Mp; m += THREADS) {
+                    a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
+                    if (a.exact) a.R[m] = yrow[m];                     // r = y - A 0
+                }
+            }
+        }
+    } else {
+        // ---- take the signal over from the lockstep loop: K, lambda, its slice of c and of the membership; CTA 0 also the active
+        // set, its direction, x on it and the inverse; then the right-hand side(s) of the next iteration
+        K = a.Kcurv[s];
+        lam = a.lamv[s];
+        const uint32_t* gst = a.gamv + (size_t)s * a.Kstate;
+        for (int n = a0 + tid; n < a1; n += THREADS) { s_act[n - a0] = 0u; s_c[n - a0] = a.C[(size_t)s * a.ldc + n]; }
+        __syncthreads();
+        for (int k = tid; k < K; k += THREADS) { const int gi = (int)gst[k]; if (gi >= a0 && gi < a1) s_act[gi - a0] = 1u; }
+        if (cta == 0) {
+            for (int k = tid; k < K; k += THREADS) { const uint32_t gi = gst[k]; s_gam[k] = gi; s_d[k] = a.dGv[(size_t)s * a.Kstate + k]; s_x[k] = xrow[gi]; }
+            const T* gsrc = a.Ginvv + (size_t)s * a.Kstate * a.Kstate;
+            for (int e = tid; e < K * K; e += THREADS) { const int r = e / K, kk = e - r * K; s_G[(size_t)r * a.ks + kk] = gsrc[(size_t)r * a.Kstate + kk]; }
+            __syncthreads();
+            publish_rhs(K);
+        }
+        it = a.it0;
     }
     __threadfence();
     grid.sync();
 
     // ---- the loop (homotopy-cpu.cpp:236-272)
-    uint32_t it = 0;
     for (;;) {
         ++it;
         for (int m = tid; m < a.Mp; m += THREADS) { s_p[m] = __ldcg(a.P + m); if (a.exact) s_r[m] = __ldcg(a.R + m); }
@@ -234,7 +309,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         const uint32_t idx = bidx & 0x7fffffffu;
         const int Knew = present ? K - 1 : K + 1;
         if (Knew == 0) {   // :248-249
-            if (cta == 0 && tid == 0) { *a.iters = it; *a.errs = (double)lam; }
+            if (cta == 0 && tid == 0) { *it_out = it; *err_out = (double)lam; }
             break;
         }
         // c -= gamma q on the slice, |c|_inf partial (:255, :270)
@@ -266,7 +341,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         if (cta == 0) {
             const int ldm = a.ks;
             // x += gamma * d with the OLD direction (:252), multiply and add rounded separately (see homotopy_scan_kernel)
-            for (int k = tid; k < K; k += THREADS) { const T xv = add_rn(s_x[k], mul_rn(gamma, s_d[k])); s_x[k] = xv; a.x[s_gam[k]] = xv; }
+            for (int k = tid; k < K; k += THREADS) { const T xv = add_rn(s_x[k], mul_rn(gamma, s_d[k])); s_x[k] = xv; xrow[s_gam[k]] = xv; }
             int slot = -1;
             if (present) { for (int k = 0; k < K; ++k) if (s_gam[k] == idx) slot = k; }
             const int ncg = K + (present ? 0 : 1);
@@ -292,7 +367,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     s_G[(size_t)r * ldm + K] = u3;
                     s_G[(size_t)K * ldm + r] = u3;
                 }
-                if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = a.x[idx]; }
+                if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = xrow[idx]; }
             } else {
                 // online_inverse.h:253-293; the leaving atom sits in slot j
                 const int j = slot;
@@ -324,45 +399,16 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             __syncthreads();
             matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
             __syncthreads();
-            if (cont) {   // p = A_G d (:112-116), k ascending per element as write_rhs; exact mode: r = y - A_G x_G (:94-96)
-                for (int m0 = tid * V; m0 < a.Mp; m0 += THREADS * V) {
-                    T acc[V], accr[V];
-#pragma unroll
-                    for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
-                    int k = 0;
-                    for (; k + 8 <= Knew; k += 8) {   // eight rows in flight per thread: this loop is L2 latency on ONE CTA
-                        T av8[8][V];
-#pragma unroll
-                        for (int u = 0; u < 8; ++u)
-                            *reinterpret_cast<int4*>(av8[u]) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k + u] * a.Mp + m0));
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            const T dk = s_d[k + u], xk = s_x[k + u];
-#pragma unroll
-                            for (int e = 0; e < V; ++e) { acc[e] += av8[u][e] * dk; accr[e] += av8[u][e] * xk; }
-                        }
-                    }
-                    for (; k < Knew; ++k) {
-                        T av[V];
-                        *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k] * a.Mp + m0));
-                        const T dk = s_d[k], xk = s_x[k];
-#pragma unroll
-                        for (int e = 0; e < V; ++e) { acc[e] += av[e] * dk; accr[e] += av[e] * xk; }
-                    }
-                    *reinterpret_cast<int4*>(a.P + m0) = *reinterpret_cast<const int4*>(acc);
-                    if (a.exact) {
-#pragma unroll
-                        for (int e = 0; e < V; ++e) accr[e] = a.y[m0 + e] - accr[e];    // y is zero padded to Mp
-                        *reinterpret_cast<int4*>(a.R + m0) = *reinterpret_cast<const int4*>(accr);
-                    }
-                }
-            } else if (tid == 0) { *a.iters = it; *a.errs = (double)lam_new; }   // :274
+            if (cont) publish_rhs(Knew);
+            else if (tid == 0) { *it_out = it; *err_out = (double)lam_new; }   // :274
         }
         K = Knew;
         lam = lam_new;
         if (!cont) break;
         __threadfence();
         grid.sync();
+    }
+    if (si + 1 < nsig) { __threadfence(); grid.sync(); }   // scratch and shared memory are reused by the next signal
     }
 }
 
