@@ -34,9 +34,10 @@ if traffic_out:
             return "contract_x3_pair_kernel"
         if "homotopy_algebra_kernel" in n:
             return "homotopy_algebra_kernel"
-        m = re.search(r"homotopy_scan_kernel<[^>]*,\s*(\(bool\))?(\w+)>", n)
+        m = re.search(r"homotopy_scan_kernel<([^>]*)>", n)   # <T, THREADS, NCH, GRAMQ, EXACT>
         if m:
-            return "homotopy_scan_kernel (q from Gram rows)" if m.group(2) in ("1", "true") else "homotopy_scan_kernel (Q streamed)"
+            par = [p.replace("(bool)", "").strip() for p in m.group(1).split(",")]
+            return "homotopy_scan_kernel (q from Gram rows)" if par[3] in ("1", "true") else "homotopy_scan_kernel (Q streamed)"
         return None
     cfg_name = sys.argv[sys.argv.index("--config") + 1] if "--config" in sys.argv else "C2"
     whole = json.load(open(traffic_out)) if os.path.exists(traffic_out) else {}
