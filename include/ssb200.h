@@ -210,6 +210,19 @@ int ssb200_compress_rows_dev_f64(const double* dX, size_t batch, size_t n, size_
                                  int32_t* d_count, int device, void* stream);
 int ssb200_norm_l1_f32(float* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
 int ssb200_norm_l1_f64(double* A, size_t m, size_t n, ptrdiff_t row_stride, ptrdiff_t col_stride, int device);
+/* ss::norm_l1 on a DEVICE matrix (dA: m x n row-major with leading dimension lda, normalised in place), allocating NOTHING.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The only scratch -- the n column sums -- is a
+ * static __device__ array of SSB200_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until the process exits, so
+ * n * sizeof(element) may not exceed it (n <= 262144 float32 / 131072 float64 columns): larger matrices are refused with
+ * SSB200_INVALID_ARGUMENT and the message names the limit.  The call makes no cudaMalloc / cudaFree / allocating library
+ * call; it enqueues two kernels on `stream` (a cudaStream_t of `device`, NULL = the default stream) and returns WITHOUT
+ * synchronising.  All calls on one GPU share the scratch array: calls that overlap on the GPU race on it -- keep them on one
+ * stream or order them with events.  Nothing in the array has to start at zero (every slot read was written by the same
+ * call).  The column sums are formed in the row order of ssb200_norm_l1_*, so both entries give the same values. */
+#define SSB200_NOALLOC_SCRATCH_BYTES (1 << 20)
+int ssb200_norm_l1_dev_noalloc_f32(float* dA, size_t m, size_t n, size_t lda, int device, void* stream);
+int ssb200_norm_l1_dev_noalloc_f64(double* dA, size_t m, size_t n, size_t lda, int device, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Instrumentation (bench.py / tests; not part of the reference API).

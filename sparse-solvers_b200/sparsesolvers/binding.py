@@ -15,7 +15,7 @@ import numpy as np
 from ._lib import SolverError, check, lib
 
 __all__ = ["Homotopy", "HomotopyGroup", "Irls", "HomotopyReport", "IrlsReport", "version", "SolverError",
-           "reconstruct_signal", "norm_l1", "fp64_peak"]
+           "reconstruct_signal", "norm_l1", "norm_l1_noalloc", "NOALLOC_SCRATCH_BYTES", "fp64_peak"]
 
 
 def version():
@@ -458,3 +458,23 @@ def norm_l1(A, device=0):
     check(getattr(lib(), f"ssb200_norm_l1_{sfx}")(_ptr(A), C.c_size_t(A.shape[0]), C.c_size_t(A.shape[1]),
                                                    C.c_ssize_t(rs), C.c_ssize_t(cs), C.c_int(device)))
     return A
+
+
+NOALLOC_SCRATCH_BYTES = 1 << 20   # include/ssb200.h: SSB200_NOALLOC_SCRATCH_BYTES
+
+
+def norm_l1_noalloc(dA, stream=None):
+    """ss::norm_l1 in place on a DEVICE matrix (torch CUDA tensor, 2-D, unit column stride) through the entry that allocates
+    nothing (ssb200_norm_l1_dev_noalloc_*; no counterpart in the reference).  The column sums live in a static device array of
+    NOALLOC_SCRATCH_BYTES, so at most that many bytes of columns; queued on `stream` (default: torch's current stream) and NOT
+    synchronised; calls that overlap on one GPU race on the scratch array."""
+    import torch
+    dt = {torch.float32: np.dtype(np.float32), torch.float64: np.dtype(np.float64)}.get(dA.dtype)
+    if dt is None or dA.dim() != 2 or not dA.is_cuda or dA.stride(1) != 1:
+        raise TypeError("dA must be a 2-D float32/float64 CUDA tensor with unit column stride")
+    sfx, _ = _SFX[dt]
+    if stream is None:
+        stream = torch.cuda.current_stream(dA.device).cuda_stream
+    check(getattr(lib(), f"ssb200_norm_l1_dev_noalloc_{sfx}")(C.c_void_p(dA.data_ptr()), C.c_size_t(dA.shape[0]), C.c_size_t(dA.shape[1]),
+                                                               C.c_size_t(dA.stride(0)), C.c_int(dA.device.index or 0), C.c_void_p(stream)))
+    return dA

@@ -6,6 +6,6 @@ cd "$(dirname "$0")/../sparse-solvers_b200/csrc"
 out=../../build/variants/$1
 mkdir -p "$out"
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC $2 -c capi.cu -o "$out/capi.o" 2>/dev/null
-nvcc -shared -o "$out/libssb200.so" "$out/capi.o" contract_tc.o
+nvcc -shared -o "$out/libssb200.so" "$out/capi.o" contract_tc.o noalloc.o
 rm -f "$out/capi.o"
 echo "$out/libssb200.so"
