@@ -370,6 +370,19 @@ int ssb200_homotopy_get_residual_info(void* h, int* mode_in_effect, double* cohe
                        else { auto* s = static_cast<Homotopy<double>*>(b); ex = s->exact_residual(); mu = s->coherence(); }
                        if (mode_in_effect) *mode_in_effect = ex ? SSB200_RESIDUAL_EXACT : SSB200_RESIDUAL_INCREMENTAL;
                        if (coherence) *coherence = mu; }); }
+#if SSB_SINGLE_PROF
+// variant builds only (tools/single_prof.py): the phase timer of the single-signal kernel, read and cleared
+int ssb200_debug_single_profile(uint64_t out[16])
+{
+    return guarded([&] {
+        unsigned long long h[16], z[16] = {};
+        SSB_CUDA(cudaMemcpyFromSymbol(h, g_single_prof, sizeof(h)));
+        SSB_CUDA(cudaMemcpyToSymbol(g_single_prof, z, sizeof(z)));
+        for (int i = 0; i < 16; ++i) out[i] = h[i];
+    });
+}
+#endif
+
 int ssb200_fp64_peak_probe(int device, int kind, double* tflops)
 { return guarded([&] { SSB_REQUIRE(tflops && (kind == 0 || kind == 1), "bad arguments");
                        require_sm100(device); device_guard g(device);

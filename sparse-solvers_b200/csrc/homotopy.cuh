@@ -353,6 +353,9 @@ private:
     // one signal: the whole solve in one cooperative kernel (homotopy_single.cuh); false = shape not supported
     bool solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters, double* errs,
                       bool reports_on_host);
+    // the same kernel as thread-block clusters (one cluster per signal, `nclusters` signals at a time): fills a.cnt and launches on
+    // `st`; false = does not apply (dictionary too large to stream through one cluster, device refuses the cluster, SSB200_CLUSTER=0)
+    bool launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStream_t st);
     dev_buffer single_ws_;
     pinned_buffer single_rep_;
     template <typename F> void run_lanes(int nlanes, size_t nchunks, F&& body);

@@ -209,15 +209,19 @@ static void launch_step(int threads, int nch, bool gs, unsigned grid, size_t sme
 template <typename T>
 static void launch_scan(int threads, int nch, bool gram, unsigned grid, cudaStream_t st, const HomArgs<T>& a, int kb)
 {
+    static const bool one_slot_off = [] { const char* e = getenv("SSB200_SCAN_KR3"); return e && atoi(e) != 0; }();   // A/B switch
+#define SSB_SCAN_KR(TH, NC, KR)                                                                   \
+        if (a.exact) { if (gram) homotopy_scan_kernel<T, TH, NC, true, true, KR><<<grid, TH, 0, st>>>(a, kb);     \
+                       else      homotopy_scan_kernel<T, TH, NC, false, true, KR><<<grid, TH, 0, st>>>(a, kb); } \
+        else         { if (gram) homotopy_scan_kernel<T, TH, NC, true, false, KR><<<grid, TH, 0, st>>>(a, kb);    \
+                       else      homotopy_scan_kernel<T, TH, NC, false, false, KR><<<grid, TH, 0, st>>>(a, kb); }
 #define SSB_SCAN(TH, NC)                                                                          \
     if (threads == TH && nch == NC) {                                                             \
-        if (a.exact) { if (gram) homotopy_scan_kernel<T, TH, NC, true, true><<<grid, TH, 0, st>>>(a, kb);     \
-                       else      homotopy_scan_kernel<T, TH, NC, false, true><<<grid, TH, 0, st>>>(a, kb); } \
-        else         { if (gram) homotopy_scan_kernel<T, TH, NC, true, false><<<grid, TH, 0, st>>>(a, kb);    \
-                       else      homotopy_scan_kernel<T, TH, NC, false, false><<<grid, TH, 0, st>>>(a, kb); } \
+        if (kb <= TH && !one_slot_off) { SSB_SCAN_KR(TH, NC, 1) } else { SSB_SCAN_KR(TH, NC, 3) }  \
         SSB_CUDA(cudaGetLastError()); return; }
     SSB_SCAN(128, 1) SSB_SCAN(128, 2) SSB_SCAN(128, 4) SSB_SCAN(256, 1) SSB_SCAN(256, 2) SSB_SCAN(256, 4) SSB_SCAN(256, 0)
 #undef SSB_SCAN
+#undef SSB_SCAN_KR
     throw invalid_argument{ "no scan-kernel variant for this shape" };
 }
 
@@ -541,6 +545,55 @@ void Homotopy<T>::run_lanes(int nlanes, size_t nchunks, F&& body)
 }
 
 
+// Cluster form of the single-signal kernel.  A cluster of 16 (8 where the device refuses the non-portable size) owns a signal: an
+// iteration's three barriers are barrier.cluster instead of grid.sync over 148 CTAs, which is most of what an iteration cost.
+// The dictionary streams from L2 through the cluster's SMs only, so it applies while that is cheap (<= 8 MB: C1 1 MB, C2 4 MB).
+template <typename T>
+bool Homotopy<T>::launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStream_t st)
+{
+    if (const char* e = getenv("SSB200_CLUSTER")) if (atoi(e) == 0) return false;                      // tuning knob / A-B switch
+    if ((size_t)Npad * Mp * sizeof(T) > ((size_t)8 << 20)) return false;
+    constexpr int THREADS = 256;
+    auto fn = homotopy_single_kernel<T, THREADS, true>;
+    static std::atomic<uint64_t> smem_done{ 0 }, nonportable_done{ 0 };
+    int want = SINGLE_CLUSTER_MAX;
+    if (const char* e = getenv("SSB200_CLUSTER_SIZE")) want = std::max(2, std::min(SINGLE_CLUSTER_MAX, atoi(e)));
+    for (int cs = want; cs >= 2; cs >>= 1) {
+        const int cnt = (Npad + cs - 1) / cs;
+        // the CTA's slice of the dictionary rides in shared memory when it fits (C1: 64 KB per CTA of a 16-cluster)
+        int dict = 1;
+        if (const char* e = getenv("SSB200_CLUSTER_DICT")) dict = atoi(e) != 0;
+        size_t smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, dict != 0);
+        if (smem > 200 * 1024) { dict = 0; smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, false); }
+        if (smem > 200 * 1024) continue;
+        if (smem > 48 * 1024) optin_shared_memory((const void*)fn, smem_done);
+        if (cs > 8) {
+            const uint64_t bit = 1ull << (device & 63);
+            if (!(nonportable_done.load(std::memory_order_acquire) & bit)) {
+                if (cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); continue; }
+                nonportable_done.fetch_or(bit, std::memory_order_release);
+            }
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(cs * nclusters));
+        cfg.blockDim = dim3(THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int fit = 0;
+        if (cudaOccupancyMaxActiveClusters(&fit, (const void*)fn, &cfg) != cudaSuccess || fit < 1) { cudaGetLastError(); continue; }
+        a.cnt = cnt;
+        a.dict_smem = dict;
+        SSB_CUDA(cudaLaunchKernelEx(&cfg, fn, a));
+        return true;
+    }
+    return false;
+}
+
 template <typename T>
 bool Homotopy<T>::launch_finisher(Lane& L, const HomArgs<T>& h, uint32_t it0, const int* d_act, const int* d_count)
 {
@@ -557,7 +610,7 @@ bool Homotopy<T>::launch_finisher(Lane& L, const HomArgs<T>& h, uint32_t it0, co
     const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
     if (smem > 200 * 1024) return false;
     static std::atomic<uint64_t> configured{ 0 };
-    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS>, configured);
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS, false>, configured);
     // scratch: P | R | Cg | part_t | part_max | part_i
     const size_t nT = (size_t)2 * Mp + Npad + 2 * (size_t)grid + 8;
     L.fin_ws.reserve(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64);
@@ -574,10 +627,13 @@ bool Homotopy<T>::launch_finisher(Lane& L, const HomArgs<T>& h, uint32_t it0, co
     a.itersv = h.iters; a.errsv = h.errs;
     void* params[] = { &a };
     nvtx_range nv("ssb200 finisher (stragglers to the end)");
-    // a cooperative grid needs every SM: two lanes launching one each could each hold half the machine and wait forever
-    std::lock_guard<std::mutex> g(coop_mu_);
+    // one cluster per straggler, side by side (an ordinary launch); else the cooperative grid, which needs every SM: two lanes
+    // launching one each could each hold half the machine and wait forever, hence one at a time per handle
     const int span = L.begin(timing, 5);
-    SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS>, dim3((unsigned)grid), dim3(THREADS), params, smem, L.stream));
+    if (!launch_single_cluster(a, FIN_MAX, L.stream)) {
+        std::lock_guard<std::mutex> g(coop_mu_);
+        SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS, false>, dim3((unsigned)grid), dim3(THREADS), params, smem, L.stream));
+    }
     L.end(span);
     L.counters[0]++;
     SSB_CUDA(cudaStreamSynchronize(L.stream));
@@ -602,7 +658,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
     if (smem > 200 * 1024) return false;
     static std::atomic<uint64_t> configured{ 0 };
-    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS>, configured);
+    if (smem > 48 * 1024) optin_shared_memory((const void*)homotopy_single_kernel<T, THREADS, false>, configured);
     Lane& L = lane(0);
     cudaStream_t st = L.stream;
     // workspace: y (padded) | P | R | Cg | x | part_t | part_max | part_i | iters | errs
@@ -625,7 +681,8 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     void* params[] = { &a };
     const int span = L.begin(timing, 1);
     nvtx_range nv("ssb200 single-signal solve");
-    SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS>, dim3((unsigned)grid), dim3(THREADS), params, smem, st));
+    if (!launch_single_cluster(a, 1, st))
+    SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS, false>, dim3((unsigned)grid), dim3(THREADS), params, smem, st));
     L.end(span);
     L.counters[0]++;
     if (x_on_host) SSB_CUDA(cudaMemcpyAsync(x, d_x, (size_t)N * sizeof(T), cudaMemcpyDeviceToHost, st));

@@ -19,6 +19,18 @@
 
 namespace ssb {
 
+// phase timer of the loop as CTA 0 / thread 0 sees it (variant build -DSSB_SINGLE_PROF=1, tools/single_prof.py): clock64 deltas
+// summed per phase into g_single_prof, slot 15 counts iterations
+#ifndef SSB_SINGLE_PROF
+#define SSB_SINGLE_PROF 0
+#endif
+#if SSB_SINGLE_PROF
+__device__ unsigned long long g_single_prof[16];
+#define SSB_PROF(i) do { if (threadIdx.x == 0 && cta == 0) { const long long t_ = clock64(); g_single_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = t_; } } while (0)
+#else
+#define SSB_PROF(i) do {} while (0)
+#endif
+
 template <typename T>
 struct SingleArgs {
     int N, Npad, Mp, Kmax, ks;
@@ -33,6 +45,7 @@ struct SingleArgs {
     uint32_t* iters; double* errs;
     T tol; uint32_t max_iter;
     int cnt;              // atoms per CTA
+    int dict_smem;        // 1: every CTA keeps its slice of the dictionary (cnt x Mp) in shared memory for the whole launch
     // ---- resume mode: the finisher of the lockstep loop.  The last few still-running signals of a chunk (stragglers that go on
     // to max_iterations long after the rest has converged) are taken from their lockstep state to the end here, one after the
     // other: an iteration then costs grid barriers instead of two thin launches and a host round trip.
@@ -49,16 +62,23 @@ struct SingleArgs {
 };
 
 template <typename T>
-inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks) {
+inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks, bool dict_slice = false) {
     const size_t KC = (size_t)((Kmax + 2) & ~1);
-    return (2 * (size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64;
+    return (2 * (size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64 +
+           (dict_slice ? (size_t)cnt * Mp * sizeof(T) + 16 : 0);
 }
 
-template <typename T, int THREADS>
+constexpr int SINGLE_CLUSTER_MAX = 16;   // CTAs of a cluster (16 needs the non-portable opt-in, 8 is portable)
+
+// CLUSTER = false: a cooperative grid, one CTA per SM, barriers are grid.sync() and the exchange goes through global scratch.
+// CLUSTER = true:  one thread-block cluster per signal (grid = clusters x cluster size, an ordinary launch); barriers are
+//                  barrier.cluster (~0.2 us against ~2 us), the partials are PUSHED into every CTA's shared memory, the right-hand
+//                  sides are read from CTA 0's shared memory and c at the active atoms from its owner's (distributed shared memory):
+//                  no global scratch, no fence.  Same arithmetic, same order: results are the same bits.
+template <typename T, int THREADS, bool CLUSTER>
 __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> a)
 {
     namespace cg = cooperative_groups;
-    cg::grid_group grid = cg::this_grid();
     constexpr int V = 16 / sizeof(T);
     constexpr int NW = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -66,6 +86,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     __shared__ uint32_t red_i[NW];
     __shared__ T sh_gamma, sh_lam;
     __shared__ uint32_t sh_idx;
+    __shared__ T xp_t[SINGLE_CLUSTER_MAX], xp_max[SINGLE_CLUSTER_MAX];     // cluster mode: the partials of every CTA, pushed by their owners
+    __shared__ uint32_t xp_i[SINGLE_CLUSTER_MAX + 1];
 
     const int KC = (a.Kmax + 2) & ~1;
     T* s_p = reinterpret_cast<T*>(smem_raw);          // [Mp]
@@ -82,39 +104,100 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     uint32_t* s_gam = s_act + a.cnt;                  // [KC]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cta = blockIdx.x, G = gridDim.x;
+    int cta = blockIdx.x, G = gridDim.x, cid = 0, ncl = 1;
+    if constexpr (CLUSTER) {
+        cg::cluster_group cl = cg::this_cluster();
+        cta = (int)cl.block_rank(); G = (int)cl.num_blocks(); cid = blockIdx.x / G; ncl = gridDim.x / G;
+    }
+    // barrier over the CTAs that share a signal; what was written before it is visible after it
+    auto sync_all = [&]() {
+        if constexpr (CLUSTER) cg::this_cluster().sync();
+        else { __threadfence(); cg::this_grid().sync(); }
+    };
+    // partials: (value, index) and |c|_inf per CTA; slot G of the index array carries the membership of atom 0
+    auto put_pair = [&](int slot, T v, uint32_t i) {          // one thread
+        if constexpr (CLUSTER) {
+            cg::cluster_group cl = cg::this_cluster();
+            for (int g = 0; g < G; ++g) { cl.map_shared_rank(xp_t, g)[slot] = v; cl.map_shared_rank(xp_i, g)[slot] = i; }
+        } else { a.part_t[slot] = v; a.part_i[slot] = i; }
+    };
+    auto put_index = [&](int slot, uint32_t i) {
+        if constexpr (CLUSTER) { cg::cluster_group cl = cg::this_cluster(); for (int g = 0; g < G; ++g) cl.map_shared_rank(xp_i, g)[slot] = i; }
+        else a.part_i[slot] = i;
+    };
+    auto put_max = [&](int slot, T v) {
+        if constexpr (CLUSTER) { cg::cluster_group cl = cg::this_cluster(); for (int g = 0; g < G; ++g) cl.map_shared_rank(xp_max, g)[slot] = v; }
+        else a.part_max[slot] = v;
+    };
+    auto get_t = [&](int g) -> T { if constexpr (CLUSTER) return xp_t[g]; else return __ldcg(a.part_t + g); };
+    auto get_i = [&](int g) -> uint32_t { if constexpr (CLUSTER) return xp_i[g]; else return __ldcg(a.part_i + g); };
+    auto get_max = [&](int g) -> T { if constexpr (CLUSTER) return xp_max[g]; else return __ldcg(a.part_max + g); };
+    // where CTA 0 leaves the right-hand sides of the next iteration: its own s_p / s_r (read by the others through DSMEM) or global
+    T* const outP = CLUSTER ? s_p : a.P;
+    T* const outR = CLUSTER ? s_r : a.R;
     const int a0 = cta * a.cnt, a1 = min(a.Npad, a0 + a.cnt);
     const T TMAX = num_traits<T>::max();
 
-    // q over the slice: one warp per atom, lanes stride the row in 16-byte pieces, warp_sum (contract_gemv_kernel)
+    // the CTA's slice of the dictionary: shared memory when it fits (cluster form: 1/16 of the atoms), else streamed from L2
+    const T* dict = a.At + (size_t)a0 * a.Mp;                      // row of atom n: dict + (n - a0) * Mp
+    if (a.dict_smem) {
+        T* s_A = reinterpret_cast<T*>((reinterpret_cast<uintptr_t>(s_gam + KC) + 15) & ~(uintptr_t)15);
+        const int n16 = max(0, a1 - a0) * (a.Mp / V);
+        const int4* src = reinterpret_cast<const int4*>(dict);
+        for (int i = tid; i < n16; i += THREADS) reinterpret_cast<int4*>(s_A)[i] = __ldg(src + i);
+        __syncthreads();
+        dict = s_A;
+    }
+    // q over the slice: one warp per atom, lanes stride the row in 16-byte pieces, warp_sum (contract_gemv_kernel: the same sum
+    // per atom in the same order); a warp keeps the rows of CB atoms in flight (a slice is 8 atoms per CTA as a grid, 64 as a cluster)
+    constexpr int CB = 4;
     auto correlate = [&](const T* rhs) {
-        for (int n = a0 + warp; n < a1; n += NW) {
-            const T* row = a.At + (size_t)n * a.Mp;
-            T acc = T(0);
-            for (int m = lane * V; m < a.Mp; m += 32 * V) {
-                T av[V];
-                *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(row + m));
+        for (int nb = a0 + warp; nb < a1; nb += NW * CB) {
+            T acc[CB];
 #pragma unroll
-                for (int v = 0; v < V; ++v) acc += av[v] * rhs[m + v];
+            for (int u = 0; u < CB; ++u) acc[u] = T(0);
+            for (int m = lane * V; m < a.Mp; m += 32 * V) {
+                T av[CB][V];
+#pragma unroll
+                for (int u = 0; u < CB; ++u) {
+                    const int n = min(nb + u * NW, a1 - 1);
+                    *reinterpret_cast<int4*>(av[u]) = *reinterpret_cast<const int4*>(dict + (size_t)(n - a0) * a.Mp + m);
+                }
+#pragma unroll
+                for (int u = 0; u < CB; ++u)
+#pragma unroll
+                    for (int v = 0; v < V; ++v) acc[u] += av[u][v] * rhs[m + v];
             }
-            acc = warp_sum(acc);
-            if (lane == 0) s_q[n - a0] = acc;
+#pragma unroll
+            for (int u = 0; u < CB; ++u) {
+                const T t = warp_sum(acc[u]);
+                if (lane == 0 && nb + u * NW < a1) s_q[nb + u * NW - a0] = t;
+            }
         }
     };
     // exact mode: c' = A^T r and q = A^T p over the slice from one pass over its atoms
     auto correlate2 = [&]() {
-        for (int n = a0 + warp; n < a1; n += NW) {
-            const T* row = a.At + (size_t)n * a.Mp;
-            T accq = T(0), accc = T(0);
-            for (int m = lane * V; m < a.Mp; m += 32 * V) {
-                T av[V];
-                *reinterpret_cast<int4*>(av) = __ldg(reinterpret_cast<const int4*>(row + m));
+        for (int nb = a0 + warp; nb < a1; nb += NW * CB) {
+            T accq[CB], accc[CB];
 #pragma unroll
-                for (int v = 0; v < V; ++v) { accq += av[v] * s_p[m + v]; accc += av[v] * s_r[m + v]; }
+            for (int u = 0; u < CB; ++u) { accq[u] = T(0); accc[u] = T(0); }
+            for (int m = lane * V; m < a.Mp; m += 32 * V) {
+                T av[CB][V];
+#pragma unroll
+                for (int u = 0; u < CB; ++u) {
+                    const int n = min(nb + u * NW, a1 - 1);
+                    *reinterpret_cast<int4*>(av[u]) = *reinterpret_cast<const int4*>(dict + (size_t)(n - a0) * a.Mp + m);
+                }
+#pragma unroll
+                for (int u = 0; u < CB; ++u)
+#pragma unroll
+                    for (int v = 0; v < V; ++v) { accq[u] += av[u][v] * s_p[m + v]; accc[u] += av[u][v] * s_r[m + v]; }
             }
-            accq = warp_sum(accq);
-            accc = warp_sum(accc);
-            if (lane == 0) { s_q[n - a0] = accq; s_c[n - a0] = accc; }
+#pragma unroll
+            for (int u = 0; u < CB; ++u) {
+                const T tq = warp_sum(accq[u]), tc = warp_sum(accc[u]);
+                if (lane == 0 && nb + u * NW < a1) { s_q[nb + u * NW - a0] = tq; s_c[nb + u * NW - a0] = tc; }
+            }
         }
     };
     // block-wide lexicographic min of (value, index); bit 31 of the index may carry the leave flag
@@ -129,7 +212,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     };
 
     const int nsig = a.resume ? min(*a.count, a.max_sigs) : 1;
-    for (int si = 0; si < nsig; ++si) {
+    for (int si = cid; si < nsig; si += ncl) {
     const int s = a.resume ? (a.act ? a.act[si] : si) : 0;
     T* xrow = a.resume ? a.X + (size_t)s * a.ldx : a.x;
     const T* yrow = a.resume ? a.Y + (size_t)s * a.ldy : a.y;
@@ -165,11 +248,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
 #pragma unroll
                         for (int e = 0; e < V; ++e) { acc[e] += av[e] * dk; accr[e] += av[e] * xk; }
                     }
-                    *reinterpret_cast<int4*>(a.P + m0) = *reinterpret_cast<const int4*>(acc);
+                    *reinterpret_cast<int4*>(outP + m0) = *reinterpret_cast<const int4*>(acc);
                     if (a.exact) {
 #pragma unroll
                         for (int e = 0; e < V; ++e) accr[e] = (m0 + e < ylen ? yrow[m0 + e] : T(0)) - accr[e];
-                        *reinterpret_cast<int4*>(a.R + m0) = *reinterpret_cast<const int4*>(accr);
+                        *reinterpret_cast<int4*>(outR + m0) = *reinterpret_cast<const int4*>(accr);
                     }
                 }
     };
@@ -192,17 +275,17 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             __syncthreads();
             if (tid == 0) {
                 for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
-                a.part_t[cta] = best; a.part_i[cta] = bidx;
-                if (cta == 0) a.part_max[0] = fabs(s_q[0]);
+                put_pair(cta, best, bidx);
+                if (cta == 0) put_max(0, fabs(s_q[0]));
             }
         }
-        grid.sync();
+        sync_all();
         K = 1;
         {
             T best = T(-1);
             uint32_t bidx = 0xffffffffu;
             for (int g = tid; g < G; g += THREADS) {
-                const T v = a.part_t[g]; const uint32_t i = a.part_i[g];
+                const T v = get_t(g); const uint32_t i = get_i(g);
                 if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
             }
             warp_argmax_first(best, bidx);
@@ -210,7 +293,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             __syncthreads();
             best = red_v[0]; bidx = red_i[0];
             for (int w = 1; w < NW; ++w) if (red_v[w] > best || (red_v[w] == best && red_i[w] < bidx)) { best = red_v[w]; bidx = red_i[w]; }
-            if (bidx == 0xffffffffu) { bidx = 0; best = a.part_max[0]; }   // all-NaN correlations
+            if (bidx == 0xffffffffu) { bidx = 0; best = get_max(0); }   // all-NaN correlations
             lam = best;
             if ((int)bidx >= a0 && (int)bidx < a1 && tid == 0) s_act[bidx - a0] = 1u;
             if (cta == 0) {
@@ -222,8 +305,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                 __syncthreads();
                 const T d0 = s_d[0];
                 for (int m = tid; m < a.Mp; m += THREADS) {
-                    a.P[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
-                    if (a.exact) a.R[m] = yrow[m];                     // r = y - A 0
+                    outP[m] = T(0) + a.At[(size_t)s_gam[0] * a.Mp + m] * d0;
+                    if (a.exact) outR[m] = yrow[m];                    // r = y - A 0
                 }
             }
         }
@@ -245,27 +328,38 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         }
         it = a.it0;
     }
-    __threadfence();
-    grid.sync();
+    sync_all();
 
     // ---- the loop (homotopy-cpu.cpp:236-272)
+    [[maybe_unused]] long long prof_t = clock64();
     for (;;) {
         ++it;
-        for (int m = tid; m < a.Mp; m += THREADS) { s_p[m] = __ldcg(a.P + m); if (a.exact) s_r[m] = __ldcg(a.R + m); }
+        SSB_PROF(14);
+        if constexpr (CLUSTER) {
+            if (cta != 0) {
+                cg::cluster_group cl = cg::this_cluster();
+                const T* rp = cl.map_shared_rank(s_p, 0);
+                const T* rr = cl.map_shared_rank(s_r, 0);
+                for (int m = tid; m < a.Mp; m += THREADS) { s_p[m] = rp[m]; if (a.exact) s_r[m] = rr[m]; }
+            }
+        } else {
+            for (int m = tid; m < a.Mp; m += THREADS) { s_p[m] = __ldcg(a.P + m); if (a.exact) s_r[m] = __ldcg(a.R + m); }
+        }
         __syncthreads();
+        SSB_PROF(0);
         if (a.exact) correlate2(); else correlate(s_p);
         __syncthreads();
+        SSB_PROF(1);
         if (a.exact) {   // lambda = |c'|_inf over the re-formed correlations (:270 on :255's c)
             T mx0 = T(0);
             for (int n = a0 + tid; n < a1 && n < a.N; n += THREADS) mx0 = max(mx0, fabs(s_c[n - a0]));
             mx0 = warp_max(mx0);
             if (lane == 0) red_v[warp] = mx0;
             __syncthreads();
-            if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); a.part_max[cta] = m; }
-            __threadfence();
-            grid.sync();
+            if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); put_max(cta, m); }
+            sync_all();
             T l2 = T(0);
-            for (int g = tid; g < G; g += THREADS) l2 = max(l2, __ldcg(a.part_max + g));
+            for (int g = tid; g < G; g += THREADS) l2 = max(l2, get_max(g));
             l2 = warp_max(l2);
             __syncthreads();
             if (lane == 0) red_v[warp] = l2;
@@ -291,19 +385,21 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             }
         block_argmin(best, bidx);
         if (tid == 0) {
-            a.part_t[cta] = best; a.part_i[cta] = bidx;
-            if (cta == 0) a.part_i[G] = s_act[0];       // membership of atom 0, for the no-candidate case
+            put_pair(cta, best, bidx);
+            if (cta == 0) put_index(G, s_act[0]);       // membership of atom 0, for the no-candidate case
         }
-        __threadfence();
-        grid.sync();
+        SSB_PROF(2);
+        sync_all();
+        SSB_PROF(3);
 
         best = TMAX; bidx = 0xffffffffu;
         for (int g = tid; g < G; g += THREADS) {
-            const T v = __ldcg(a.part_t + g); const uint32_t i = __ldcg(a.part_i + g);
+            const T v = get_t(g); const uint32_t i = get_i(g);
             if (cand_less(v, i & 0x7fffffffu, best, bidx & 0x7fffffffu)) { best = v; bidx = i; }
         }
         block_argmin(best, bidx);
-        if (bidx == 0xffffffffu) bidx = __ldcg(a.part_i + G) ? 0x80000000u : 0u;   // (max, 0): the caller toggles column 0 (:122-123)
+        if (bidx == 0xffffffffu) bidx = get_i(G) ? 0x80000000u : 0u;   // (max, 0): the caller toggles column 0 (:122-123)
+        SSB_PROF(4);
         const T gamma = best;
         const bool present = (bidx >> 31) != 0;
         const uint32_t idx = bidx & 0x7fffffffu;
@@ -317,19 +413,20 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         for (int n = a0 + tid; n < a1; n += THREADS) {
             const T cn = s_c[n - a0] - gamma * s_q[n - a0];
             s_c[n - a0] = cn;
-            a.Cg[n] = cn;
+            if constexpr (!CLUSTER) a.Cg[n] = cn;
             if (n < a.N) mx = max(mx, fabs(cn));
         }
         if ((int)idx >= a0 && (int)idx < a1 && tid == 0) s_act[idx - a0] ^= 1u;
         mx = warp_max(mx);
         if (lane == 0) red_v[warp] = mx;
         __syncthreads();
-        if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); a.part_max[cta] = m; }
-        __threadfence();
-        grid.sync();
+        if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); put_max(cta, m); }
+        SSB_PROF(5);
+        sync_all();
+        SSB_PROF(6);
 
         T lam_new = T(0);
-        for (int g = tid; g < G; g += THREADS) lam_new = max(lam_new, __ldcg(a.part_max + g));
+        for (int g = tid; g < G; g += THREADS) lam_new = max(lam_new, get_max(g));
         lam_new = warp_max(lam_new);
         if (lane == 0) red_v[warp] = lam_new;
         __syncthreads();
@@ -337,6 +434,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         for (int w = 1; w < NW; ++w) lam_new = max(lam_new, red_v[w]);
         __syncthreads();
         const bool cont = (it < a.max_iter) && (lam_new > a.tol);   // :272
+        SSB_PROF(7);
 
         if (cta == 0) {
             const int ldm = a.ks;
@@ -345,8 +443,13 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             int slot = -1;
             if (present) { for (int k = 0; k < K; ++k) if (s_gam[k] == idx) slot = k; }
             const int ncg = K + (present ? 0 : 1);
-            for (int k = tid; k < ncg; k += THREADS) s_cg[k] = __ldcg(a.Cg + (k < K ? s_gam[k] : idx));
+            for (int k = tid; k < ncg; k += THREADS) {
+                const int n = (int)(k < K ? s_gam[k] : idx);
+                if constexpr (CLUSTER) { const int owner = n / a.cnt; s_cg[k] = cg::this_cluster().map_shared_rank(s_c, owner)[n - owner * a.cnt]; }
+                else s_cg[k] = __ldcg(a.Cg + n);
+            }
             __syncthreads();
+            SSB_PROF(8);
             if (!present) {
                 // online_inverse.h:203-249 (bordering); the new atom takes slot K
                 for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];
@@ -394,21 +497,29 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                 }
             }
             __syncthreads();
+            SSB_PROF(9);
             // d_G = inv * sign(c_G, tol) (:259-263)
             for (int k = tid; k < Knew; k += THREADS) s_cg[k] = sign_tol(s_cg[k], a.tol);
             __syncthreads();
             matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
             __syncthreads();
+            SSB_PROF(10);
             if (cont) publish_rhs(Knew);
             else if (tid == 0) { *it_out = it; *err_out = (double)lam_new; }   // :274
         }
         K = Knew;
         lam = lam_new;
+        SSB_PROF(11);
         if (!cont) break;
-        __threadfence();
-        grid.sync();
+        sync_all();
+        SSB_PROF(12);
+#if SSB_SINGLE_PROF
+        if (tid == 0 && cta == 0) g_single_prof[15] += 1;
+#endif
     }
-    if (si + 1 < nsig) { __threadfence(); grid.sync(); }   // scratch and shared memory are reused by the next signal
+    // scratch and shared memory are reused by the next signal; in cluster mode nobody may leave (or move on) while CTA 0 still reads
+    // the others' shared memory
+    if (CLUSTER || si + 1 < nsig) sync_all();
     }
 }
 

@@ -37,7 +37,10 @@ __device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
 //   GRAMQ  q is not read from the contraction's output but formed here as q = G[:, active] d (G = A^T A, L2-resident): while
 //          the active set is small that is K rows of G per signal instead of a full 2 M N contraction, a gather of K atoms
 //          and 16 KB of Q traffic -- the host uses it for the first iterations (K <= it < gram_iters)
-template <typename T, int THREADS, int NCH, bool GRAMQ, bool EXACT>
+//   KR     active-set slots per thread: 1 while the iteration's bound kb fits the CTA (every BASELINE config but the long runs),
+//          else 3.  With 3 the slots past the first are dead weight that the 64-register cap turns into local-memory spills
+//          right behind the dependent gam -> x[gam] loads (ncu r2: STL at 24 % of the stall samples).
+template <typename T, int THREADS, int NCH, bool GRAMQ, bool EXACT, int KR = 3>
 __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homotopy_scan_kernel(HomArgs<T> a, int kb)
 {
     constexpr int GRAM_KMAX = 32;
@@ -82,7 +85,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
     }
     const int K = a.Kcur[s];
     T lam = a.lam[s];
-    constexpr int KR = 3;   // K <= KR * THREADS (checked by the host)
+    // K <= KR * THREADS (checked by the host)
     uint32_t gk[KR];
     T dk[KR], xk[KR];
 #pragma unroll

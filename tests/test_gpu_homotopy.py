@@ -105,6 +105,31 @@ def test_single_solve_equals_batch_row(ss):
         np.testing.assert_allclose(x, Xb[b], rtol=2e-4, atol=1e-6)
 
 
+@pytest.mark.parametrize("dtype,shape,k,max_iter", [(np.float32, (256, 1024), 16, 48), (np.float64, (128, 512), 8, 30), (np.float32, (512, 2048), 32, 80)])
+@pytest.mark.parametrize("mode", ["incremental", "exact"])
+def test_single_solve_cluster_form_equals_the_grid_form(ss, dtype, shape, k, max_iter, mode, monkeypatch):
+    """homotopy_single_kernel as one thread-block cluster per signal (barrier.cluster, exchange through distributed shared memory)
+    against the cooperative-grid form (grid.sync, exchange through global scratch): same arithmetic in the same order, so the
+    same bits -- coefficients, iteration counts and the reported error; also at cluster size 8 (the portable size)."""
+    from sparsesolvers import synth
+    A = synth.dictionary(*shape, dtype=dtype, seed=31)
+    Y, _ = synth.sparse_signals(A, 6, k, seed=32)
+    Y[5] = np.random.default_rng(33).standard_normal(shape[0]).astype(dtype)      # a signal that runs to max_iterations
+    s = ss.Homotopy(A)
+    s.set_residual_mode(mode)
+    got = {}
+    for form, env in (("grid", {"SSB200_CLUSTER": "0"}), ("cluster16", {"SSB200_CLUSTER": "1"}), ("cluster8", {"SSB200_CLUSTER": "1", "SSB200_CLUSTER_SIZE": "8"})):
+        monkeypatch.delenv("SSB200_CLUSTER_SIZE", raising=False)
+        for key, v in env.items():
+            monkeypatch.setenv(key, v)
+        got[form] = [s.solve(Y[b], 1e-3, max_iter) for b in range(len(Y))]
+    for form in ("cluster16", "cluster8"):
+        for (xg, rg), (xc, rc) in zip(got["grid"], got[form]):
+            assert rc.iter == rg.iter and rc.solution_error == rg.solution_error, (form, rc.iter, rg.iter)
+            np.testing.assert_array_equal(xc, xg)
+    assert max(r.iter for _, r in got["grid"]) == max_iter
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_smoke_identity(ss, dtype):
     """test_util.h:27-55, test_binding.py:9-20: x == signal exactly, iter == 1, solution_error == 0."""
