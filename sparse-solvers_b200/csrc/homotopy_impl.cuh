@@ -563,8 +563,11 @@ bool Homotopy<T>::launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStr
         // the CTA's slice of the dictionary rides in shared memory when it fits (C1: 64 KB per CTA of a 16-cluster)
         int dict = 1;
         if (const char* e = getenv("SSB200_CLUSTER_DICT")) dict = atoi(e) != 0;
-        size_t smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, dict != 0);
-        if (smem > 200 * 1024) { dict = 0; smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, false); }
+        int stage = 1;
+        if (const char* e = getenv("SSB200_CLUSTER_STAGE")) stage = atoi(e) != 0;
+        size_t smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, dict != 0, stage != 0);
+        if (smem > 200 * 1024) { dict = 0; smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, false, stage != 0); }
+        if (smem > 200 * 1024) { stage = 0; smem = homotopy_single_smem<T>(Mp, cnt, a.Kmax, a.ks, false, false); }
         if (smem > 200 * 1024) continue;
         if (smem > 48 * 1024) optin_shared_memory((const void*)fn, smem_done);
         if (cs > 8) {
@@ -588,6 +591,7 @@ bool Homotopy<T>::launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStr
         if (cudaOccupancyMaxActiveClusters(&fit, (const void*)fn, &cfg) != cudaSuccess || fit < 1) { cudaGetLastError(); continue; }
         a.cnt = cnt;
         a.dict_smem = dict;
+        a.stage = stage;
         SSB_CUDA(cudaLaunchKernelEx(&cfg, fn, a));
         return true;
     }

@@ -46,6 +46,7 @@ struct SingleArgs {
     T tol; uint32_t max_iter;
     int cnt;              // atoms per CTA
     int dict_smem;        // 1: every CTA keeps its slice of the dictionary (cnt x Mp) in shared memory for the whole launch
+    int stage;            // 1: SINGLE_STAGE_BYTES of shared memory are there for the gather of p = A_G d
     // ---- resume mode: the finisher of the lockstep loop.  The last few still-running signals of a chunk (stragglers that go on
     // to max_iterations long after the rest has converged) are taken from their lockstep state to the end here, one after the
     // other: an iteration then costs grid barriers instead of two thin launches and a host round trip.
@@ -61,11 +62,12 @@ struct SingleArgs {
     uint32_t* itersv; double* errsv;     // reports, by signal
 };
 
+constexpr int SINGLE_STAGE_BYTES = 16 * 1024;   // cluster form: the atom rows of p = A_G d pass through shared memory, 4 x 16 bytes per thread at a time
 template <typename T>
-inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks, bool dict_slice = false) {
+inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks, bool dict_slice = false, bool stage = false) {
     const size_t KC = (size_t)((Kmax + 2) & ~1);
-    return (2 * (size_t)Mp + 2 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64 +
-           (dict_slice ? (size_t)cnt * Mp * sizeof(T) + 16 : 0);
+    return (2 * (size_t)Mp + 3 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64 +
+           (stage ? SINGLE_STAGE_BYTES + 16 : 0) + (dict_slice ? (size_t)cnt * Mp * sizeof(T) + 16 : 0);
 }
 
 constexpr int SINGLE_CLUSTER_MAX = 16;   // CTAs of a cluster (16 needs the non-portable opt-in, 8 is portable)
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     __shared__ uint32_t red_i[NW];
     __shared__ T sh_gamma, sh_lam;
     __shared__ uint32_t sh_idx;
-    __shared__ T xp_t[SINGLE_CLUSTER_MAX], xp_max[SINGLE_CLUSTER_MAX];     // cluster mode: the partials of every CTA, pushed by their owners
+    __shared__ T xp_t[SINGLE_CLUSTER_MAX], xp_max[SINGLE_CLUSTER_MAX], xp_lam[SINGLE_CLUSTER_MAX];   // cluster form: the partials of every CTA, pushed by their owners
     __shared__ uint32_t xp_i[SINGLE_CLUSTER_MAX + 1];
 
     const int KC = (a.Kmax + 2) & ~1;
@@ -94,7 +96,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     T* s_r = s_p + a.Mp;                              // [Mp]   residual (exact mode)
     T* s_c = s_r + a.Mp;                              // [cnt]
     T* s_q = s_c + a.cnt;                             // [cnt]
-    T* s_G = s_q + a.cnt;                             // [(Kmax+1) * ks]   CTA 0 only from here on
+    T* s_c2 = s_q + a.cnt;                            // [cnt]  cluster form: the updated c goes here, then the two swap
+    T* s_G = s_c2 + a.cnt;                            // [(Kmax+1) * ks]   CTA 0 only from here on
     T* s_d = s_G + (size_t)(a.Kmax + 1) * a.ks;
     T* s_u1 = s_d + KC;
     T* s_u2 = s_u1 + KC;
@@ -132,6 +135,39 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     auto get_t = [&](int g) -> T { if constexpr (CLUSTER) return xp_t[g]; else return __ldcg(a.part_t + g); };
     auto get_i = [&](int g) -> uint32_t { if constexpr (CLUSTER) return xp_i[g]; else return __ldcg(a.part_i + g); };
     auto get_max = [&](int g) -> T { if constexpr (CLUSTER) return xp_max[g]; else return __ldcg(a.part_max + g); };
+    // the same inside the loop, where every thread holds the value: cluster form, thread g pushes to CTA g (G stores in flight at once)
+    auto push_pair = [&](T v, uint32_t i) {
+        if constexpr (CLUSTER) {
+            if (tid < G) { cg::cluster_group cl = cg::this_cluster(); cl.map_shared_rank(xp_t, tid)[cta] = v; cl.map_shared_rank(xp_i, tid)[cta] = i; }
+        } else if (tid == 0) { a.part_t[cta] = v; a.part_i[cta] = i; }
+    };
+    auto push_index = [&](int slot, uint32_t i) {
+        if constexpr (CLUSTER) { if (tid < G) cg::this_cluster().map_shared_rank(xp_i, tid)[slot] = i; }
+        else if (tid == 0) a.part_i[slot] = i;
+    };
+    auto push_max = [&](T v, bool lam_slot) {     // lam_slot: the exact mode's |c'|_inf exchange has its own array (one barrier less between uses)
+        if constexpr (CLUSTER) { if (tid < G) cg::this_cluster().map_shared_rank(lam_slot ? xp_lam : xp_max, tid)[cta] = v; }
+        else if (tid == 0) a.part_max[cta] = v;
+    };
+    // reductions over the CTA partials after a barrier, result in every thread.  Cluster form: <= 16 values, every warp reduces them
+    // itself -- no block barrier
+    auto reduce_max = [&](bool lam_slot) -> T {
+        if constexpr (CLUSTER) {
+            const T* src = lam_slot ? xp_lam : xp_max;
+            return warp_max(lane < G ? src[lane] : T(0));
+        } else {
+            T l = T(0);
+            for (int g = tid; g < G; g += THREADS) l = max(l, __ldcg(a.part_max + g));
+            l = warp_max(l);
+            __syncthreads();
+            if (lane == 0) red_v[warp] = l;
+            __syncthreads();
+            l = red_v[0];
+            for (int w = 1; w < NW; ++w) l = max(l, red_v[w]);
+            __syncthreads();
+            return l;
+        }
+    };
     // where CTA 0 leaves the right-hand sides of the next iteration: its own s_p / s_r (read by the others through DSMEM) or global
     T* const outP = CLUSTER ? s_p : a.P;
     T* const outR = CLUSTER ? s_r : a.R;
@@ -140,8 +176,9 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
 
     // the CTA's slice of the dictionary: shared memory when it fits (cluster form: 1/16 of the atoms), else streamed from L2
     const T* dict = a.At + (size_t)a0 * a.Mp;                      // row of atom n: dict + (n - a0) * Mp
+    T* const s_stage = a.stage ? reinterpret_cast<T*>((reinterpret_cast<uintptr_t>(s_gam + KC) + 15) & ~(uintptr_t)15) : nullptr;
     if (a.dict_smem) {
-        T* s_A = reinterpret_cast<T*>((reinterpret_cast<uintptr_t>(s_gam + KC) + 15) & ~(uintptr_t)15);
+        T* s_A = reinterpret_cast<T*>((reinterpret_cast<uintptr_t>(s_gam + KC) + 15 + (a.stage ? SINGLE_STAGE_BYTES + 16 : 0)) & ~(uintptr_t)15);
         const int n16 = max(0, a1 - a0) * (a.Mp / V);
         const int4* src = reinterpret_cast<const int4*>(dict);
         for (int i = tid; i < n16; i += THREADS) reinterpret_cast<int4*>(s_A)[i] = __ldg(src + i);
@@ -210,6 +247,21 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         warp_argmin_flagged(v, i);
         __syncthreads();
     };
+    // (gamma, idx) over the CTA partials after the barrier, in every thread
+    auto reduce_pairs = [&](T& v, uint32_t& i) {
+        if constexpr (CLUSTER) {
+            v = lane < G ? xp_t[lane] : TMAX;
+            i = lane < G ? xp_i[lane] : 0xffffffffu;
+            warp_argmin_flagged(v, i);
+        } else {
+            v = TMAX; i = 0xffffffffu;
+            for (int g = tid; g < G; g += THREADS) {
+                const T pv = __ldcg(a.part_t + g); const uint32_t pi = __ldcg(a.part_i + g);
+                if (cand_less(pv, pi & 0x7fffffffu, v, i & 0x7fffffffu)) { v = pv; i = pi; }
+            }
+            block_argmin(v, i);
+        }
+    };
 
     const int nsig = a.resume ? min(*a.count, a.max_sigs) : 1;
     for (int si = cid; si < nsig; si += ncl) {
@@ -224,6 +276,49 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     int K = 1;
     // p = A_G d (:112-116), k ascending per element as write_rhs; exact mode: r = y - A_G x_G (:94-96); CTA 0 only
     auto publish_rhs = [&](int Knew) {
+                const int tpr = a.Mp / V;                      // threads that cover one atom row in 16-byte pieces
+                if (s_stage != nullptr && tpr <= THREADS && THREADS % tpr == 0) {
+                    // every thread fetches up to four 16-byte pieces at once into the stage (all rows of a pass in flight: one L2
+                    // round trip), then the first tpr threads add them up in slot order -- the sums of the loop below, bit for bit
+                    const int rpp = THREADS / tpr, lr = tid / tpr, mq = (tid - lr * tpr) * V, SR = 4 * rpp;
+                    T acc[V], accr[V];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) { acc[e] = T(0); accr[e] = T(0); }
+                    for (int k0 = 0; k0 < Knew; k0 += SR) {
+                        const int nr = min(SR, Knew - k0);
+                        int4 piece[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int r = lr + u * rpp;
+                            if (r < nr) piece[u] = __ldg(reinterpret_cast<const int4*>(a.At + (size_t)s_gam[k0 + r] * a.Mp + mq));
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int r = lr + u * rpp;
+                            if (r < nr) *reinterpret_cast<int4*>(s_stage + (size_t)r * a.Mp + mq) = piece[u];
+                        }
+                        __syncthreads();
+                        if (tid < tpr)
+                            for (int r = 0; r < nr; ++r) {
+                                T av[V];
+                                *reinterpret_cast<int4*>(av) = *reinterpret_cast<const int4*>(s_stage + (size_t)r * a.Mp + tid * V);
+                                const T dk = s_d[k0 + r], xk = s_x[k0 + r];
+#pragma unroll
+                                for (int e = 0; e < V; ++e) { acc[e] += av[e] * dk; accr[e] += av[e] * xk; }
+                            }
+                        __syncthreads();
+                    }
+                    if (tid < tpr) {
+                        const int m0 = tid * V;
+                        *reinterpret_cast<int4*>(outP + m0) = *reinterpret_cast<const int4*>(acc);
+                        if (a.exact) {
+#pragma unroll
+                            for (int e = 0; e < V; ++e) accr[e] = (m0 + e < ylen ? yrow[m0 + e] : T(0)) - accr[e];
+                            *reinterpret_cast<int4*>(outR + m0) = *reinterpret_cast<const int4*>(accr);
+                        }
+                    }
+                    return;
+                }
                 for (int m0 = tid * V; m0 < a.Mp; m0 += THREADS * V) {
                     T acc[V], accr[V];
 #pragma unroll
@@ -356,16 +451,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             mx0 = warp_max(mx0);
             if (lane == 0) red_v[warp] = mx0;
             __syncthreads();
-            if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); put_max(cta, m); }
+            T m = red_v[0];
+            for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
+            push_max(m, true);
             sync_all();
-            T l2 = T(0);
-            for (int g = tid; g < G; g += THREADS) l2 = max(l2, get_max(g));
-            l2 = warp_max(l2);
-            __syncthreads();
-            if (lane == 0) red_v[warp] = l2;
-            __syncthreads();
-            lam = red_v[0];
-            for (int w = 1; w < NW; ++w) lam = max(lam, red_v[w]);
+            lam = reduce_max(true);
             __syncthreads();
         }
         // min-gamma search (:122-163): join candidates of the slice, leave candidates in CTA 0
@@ -384,20 +474,13 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                 if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
             }
         block_argmin(best, bidx);
-        if (tid == 0) {
-            put_pair(cta, best, bidx);
-            if (cta == 0) put_index(G, s_act[0]);       // membership of atom 0, for the no-candidate case
-        }
+        push_pair(best, bidx);
+        if (cta == 0) push_index(G, s_act[0]);      // membership of atom 0, for the no-candidate case
         SSB_PROF(2);
         sync_all();
         SSB_PROF(3);
 
-        best = TMAX; bidx = 0xffffffffu;
-        for (int g = tid; g < G; g += THREADS) {
-            const T v = get_t(g); const uint32_t i = get_i(g);
-            if (cand_less(v, i & 0x7fffffffu, best, bidx & 0x7fffffffu)) { best = v; bidx = i; }
-        }
-        block_argmin(best, bidx);
+        reduce_pairs(best, bidx);
         if (bidx == 0xffffffffu) bidx = get_i(G) ? 0x80000000u : 0u;   // (max, 0): the caller toggles column 0 (:122-123)
         SSB_PROF(4);
         const T gamma = best;
@@ -408,36 +491,37 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             if (cta == 0 && tid == 0) { *it_out = it; *err_out = (double)lam; }
             break;
         }
-        // c -= gamma q on the slice, |c|_inf partial (:255, :270)
-        T mx = T(0);
-        for (int n = a0 + tid; n < a1; n += THREADS) {
-            const T cn = s_c[n - a0] - gamma * s_q[n - a0];
-            s_c[n - a0] = cn;
-            if constexpr (!CLUSTER) a.Cg[n] = cn;
-            if (n < a.N) mx = max(mx, fabs(cn));
+        // c -= gamma q on the slice, |c|_inf partial (:255, :270).  Cluster form: into the slice's second buffer, so that CTA 0 can form
+        // c at the active atoms itself from the owners' old c and q while they are still at it -- no barrier before the algebra
+        {
+            T* const c_out = CLUSTER ? s_c2 : s_c;
+            T mx = T(0);
+            for (int n = a0 + tid; n < a1; n += THREADS) {
+                const T cn = s_c[n - a0] - gamma * s_q[n - a0];
+                c_out[n - a0] = cn;
+                if constexpr (!CLUSTER) a.Cg[n] = cn;
+                if (n < a.N) mx = max(mx, fabs(cn));
+            }
+            if ((int)idx >= a0 && (int)idx < a1 && tid == 0) s_act[idx - a0] ^= 1u;
+            mx = warp_max(mx);
+            if (lane == 0) red_v[warp] = mx;
+            __syncthreads();
+            T m = red_v[0];
+            for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
+            push_max(m, false);
         }
-        if ((int)idx >= a0 && (int)idx < a1 && tid == 0) s_act[idx - a0] ^= 1u;
-        mx = warp_max(mx);
-        if (lane == 0) red_v[warp] = mx;
-        __syncthreads();
-        if (tid == 0) { T m = red_v[0]; for (int w = 1; w < NW; ++w) m = max(m, red_v[w]); put_max(cta, m); }
         SSB_PROF(5);
-        sync_all();
-        SSB_PROF(6);
 
-        T lam_new = T(0);
-        for (int g = tid; g < G; g += THREADS) lam_new = max(lam_new, get_max(g));
-        lam_new = warp_max(lam_new);
-        if (lane == 0) red_v[warp] = lam_new;
-        __syncthreads();
-        lam_new = red_v[0];
-        for (int w = 1; w < NW; ++w) lam_new = max(lam_new, red_v[w]);
-        __syncthreads();
-        const bool cont = (it < a.max_iter) && (lam_new > a.tol);   // :272
-        SSB_PROF(7);
-
-        if (cta == 0) {
+        // x update, toggle, online inverse, new direction, next right-hand side(s): CTA 0
+        auto algebra = [&](bool publish) {
             const int ldm = a.ks;
+            // what the bordering needs from global memory is asked for first and used last
+            T pre_u1 = T(0), pre_dot = T(0), pre_x = T(0);
+            if (!present) {
+                if (tid < K) pre_u1 = a.G[(size_t)idx * a.ldg + s_gam[tid]];
+                pre_dot = a.G[(size_t)idx * a.ldg + idx];
+                if (tid == 0) pre_x = xrow[idx];
+            }
             // x += gamma * d with the OLD direction (:252), multiply and add rounded separately (see homotopy_scan_kernel)
             for (int k = tid; k < K; k += THREADS) { const T xv = add_rn(s_x[k], mul_rn(gamma, s_d[k])); s_x[k] = xv; xrow[s_gam[k]] = xv; }
             int slot = -1;
@@ -445,15 +529,20 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             const int ncg = K + (present ? 0 : 1);
             for (int k = tid; k < ncg; k += THREADS) {
                 const int n = (int)(k < K ? s_gam[k] : idx);
-                if constexpr (CLUSTER) { const int owner = n / a.cnt; s_cg[k] = cg::this_cluster().map_shared_rank(s_c, owner)[n - owner * a.cnt]; }
-                else s_cg[k] = __ldcg(a.Cg + n);
+                if constexpr (CLUSTER) {   // the owner's c and q as they stood before the step: the owner's own expression, so its bits
+                    cg::cluster_group cl = cg::this_cluster();
+                    const int owner = n / a.cnt, off = n - owner * a.cnt;
+                    const T co = cl.map_shared_rank(s_c, owner)[off], qo = cl.map_shared_rank(s_q, owner)[off];
+                    s_cg[k] = co - gamma * qo;
+                } else s_cg[k] = __ldcg(a.Cg + n);
             }
             __syncthreads();
             SSB_PROF(8);
             if (!present) {
                 // online_inverse.h:203-249 (bordering); the new atom takes slot K
-                for (int k = tid; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];
-                const T dot = a.G[(size_t)idx * a.ldg + idx];
+                if (tid < K) s_u1[tid] = pre_u1;
+                for (int k = tid + THREADS; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];
+                const T dot = pre_dot;
                 __syncthreads();
                 matvec<T, THREADS, true>(s_G, ldm, K, s_u1, s_u2, nullptr);
                 __syncthreads();
@@ -470,7 +559,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     s_G[(size_t)r * ldm + K] = u3;
                     s_G[(size_t)K * ldm + r] = u3;
                 }
-                if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = xrow[idx]; }
+                if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = pre_x; }
             } else {
                 // online_inverse.h:253-293; the leaving atom sits in slot j
                 const int j = slot;
@@ -504,15 +593,39 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
             __syncthreads();
             SSB_PROF(10);
-            if (cont) publish_rhs(Knew);
-            else if (tid == 0) { *it_out = it; *err_out = (double)lam_new; }   // :274
+            if (publish) publish_rhs(Knew);
+        };
+
+        T lam_new;
+        bool cont;
+        if constexpr (CLUSTER) {
+            // two barriers per iteration: the algebra runs beside the other CTAs' c update, its right-hand side is published -- and
+            // wasted -- even when the stop test, which needs every CTA's |c|_inf, then ends the solve
+            if (cta == 0) algebra(true);
+            { T* const t_ = s_c; s_c = s_c2; s_c2 = t_; }
+            SSB_PROF(11);
+            sync_all();
+            SSB_PROF(12);
+            lam_new = reduce_max(false);
+            cont = (it < a.max_iter) && (lam_new > a.tol);   // :272
+            if (!cont && cta == 0 && tid == 0) { *it_out = it; *err_out = (double)lam_new; }   // :274
+            SSB_PROF(7);
+        } else {
+            sync_all();
+            SSB_PROF(6);
+            lam_new = reduce_max(false);
+            cont = (it < a.max_iter) && (lam_new > a.tol);   // :272
+            SSB_PROF(7);
+            if (cta == 0) {
+                algebra(cont);
+                if (!cont && tid == 0) { *it_out = it; *err_out = (double)lam_new; }   // :274
+            }
+            SSB_PROF(11);
         }
         K = Knew;
         lam = lam_new;
-        SSB_PROF(11);
         if (!cont) break;
-        sync_all();
-        SSB_PROF(12);
+        if constexpr (!CLUSTER) { sync_all(); SSB_PROF(12); }
 #if SSB_SINGLE_PROF
         if (tid == 0 && cta == 0) g_single_prof[15] += 1;
 #endif
