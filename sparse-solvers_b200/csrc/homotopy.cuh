@@ -357,7 +357,7 @@ private:
     // `st`; false = does not apply (dictionary too large to stream through one cluster, device refuses the cluster, SSB200_CLUSTER=0)
     bool launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStream_t st);
     dev_buffer single_ws_;
-    pinned_buffer single_rep_;
+    pinned_buffer single_rep_, single_pin_;
     template <typename F> void run_lanes(int nlanes, size_t nchunks, F&& body);
 };
 

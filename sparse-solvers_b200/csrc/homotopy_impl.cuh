@@ -667,21 +667,46 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     cudaStream_t st = L.stream;
     // workspace: y (padded) | P | R | Cg | x | part_t | part_max | part_i | iters | errs
     const size_t nT = (size_t)3 * Mp + Npad + N + 2 * (size_t)grid + 8;
-    single_ws_.reserve(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64);
+    const size_t pub_off = round_up(nT * sizeof(T) + ((size_t)grid + 8) * sizeof(uint32_t) + 64, 16);   // grid form, Gram iterations: d | x | gam
+    single_ws_.reserve(pub_off + (size_t)(kmax + 2) * (2 * sizeof(T) + sizeof(uint32_t)) + 64);
     single_rep_.reserve(64);
     T* w = single_ws_.template as<T>();
     T* d_y = w; T* d_P = d_y + Mp; T* d_R = d_P + Mp; T* d_Cg = d_R + Mp; T* d_x = d_Cg + Npad; T* d_pt = d_x + N; T* d_pm = d_pt + grid;
     double* d_err = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(w) + round_up((size_t)(d_pm + grid - w) * sizeof(T), 16));
     uint32_t* d_it = reinterpret_cast<uint32_t*>(d_err + 1);
     uint32_t* d_pi = d_it + 2;
-    if (Mp > M) SSB_CUDA(cudaMemsetAsync(d_y + M, 0, (size_t)(Mp - M) * sizeof(T), st));
-    SSB_CUDA(cudaMemcpyAsync(d_y, y, (size_t)M * sizeof(T), y_on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    // host pointers: the kernel reads y from, and leaves x and the report in, one pinned buffer -- the call is a launch and a stream
+    // synchronise (staged copies of 1-4 KB to and from pageable memory were 2/3 of the 40 us a call cost beside its kernel)
+    bool zero_copy = y_on_host && x_on_host && reports_on_host;
+    if (const char* e = getenv("SSB200_ZERO_COPY")) if (atoi(e) == 0) zero_copy = false;               // A/B switch
+    unsigned char* hp = nullptr;
+    if (zero_copy) {
+        single_pin_.reserve(64 + ((size_t)Mp + N) * sizeof(T));
+        hp = single_pin_.template as<unsigned char>();
+        T* h_y = reinterpret_cast<T*>(hp + 64);
+        std::memcpy(h_y, y, (size_t)M * sizeof(T));
+        for (int m = M; m < Mp; ++m) h_y[m] = T(0);
+    } else {
+        if (Mp > M) SSB_CUDA(cudaMemsetAsync(d_y + M, 0, (size_t)(Mp - M) * sizeof(T), st));
+        SSB_CUDA(cudaMemcpyAsync(d_y, y, (size_t)M * sizeof(T), y_on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    }
     SingleArgs<T> a{};
     a.N = N; a.Npad = Npad; a.Mp = Mp; a.Kmax = kmax; a.ks = ks;
     a.At = At_; a.G = G_; a.ldg = Npad;
     a.y = d_y; a.x = x_on_host ? d_x : x; a.P = d_P; a.R = d_R; a.exact = exact_residual() ? 1 : 0; a.Cg = d_Cg; a.part_t = d_pt; a.part_i = d_pi; a.part_max = d_pm;
     a.iters = reports_on_host ? d_it : iters; a.errs = reports_on_host ? d_err : errs;
+    if (zero_copy) {
+        a.y = reinterpret_cast<T*>(hp + 64); a.ywork = d_y; a.x = d_x; a.x_out = reinterpret_cast<T*>(hp + 64) + Mp;
+        a.errs = reinterpret_cast<double*>(hp); a.iters = reinterpret_cast<uint32_t*>(hp + 8);
+    }
     a.tol = tol; a.max_iter = max_iter; a.cnt = cnt;
+    a.pub_d = reinterpret_cast<T*>(reinterpret_cast<unsigned char*>(w) + pub_off); a.pub_x = a.pub_d + (kmax + 2);
+    a.pub_gam = reinterpret_cast<uint32_t*>(a.pub_x + (kmax + 2));
+    // Gram iterations as the lockstep loop has them (solve_chunk): the first iterations of a signal are the same arithmetic on both paths
+    uint32_t gram_iters = 16;
+    if (const char* e = getenv("SSB200_GRAM_ITERS")) gram_iters = (uint32_t)std::max(0, std::min(32, atoi(e)));   // tuning knob
+    if (coherent()) gram_iters = 0;
+    a.gram_iters = std::min<uint32_t>(gram_iters, (uint32_t)kmax);
     void* params[] = { &a };
     const int span = L.begin(timing, 1);
     nvtx_range nv("ssb200 single-signal solve");
@@ -689,6 +714,12 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     SSB_CUDA(cudaLaunchCooperativeKernel((const void*)homotopy_single_kernel<T, THREADS, false>, dim3((unsigned)grid), dim3(THREADS), params, smem, st));
     L.end(span);
     L.counters[0]++;
+    if (zero_copy) {
+        SSB_CUDA(cudaStreamSynchronize(st));
+        std::memcpy(x, hp + 64 + (size_t)Mp * sizeof(T), (size_t)N * sizeof(T));
+        *errs = *reinterpret_cast<double*>(hp);
+        *iters = *reinterpret_cast<uint32_t*>(hp + 8);
+    } else {
     if (x_on_host) SSB_CUDA(cudaMemcpyAsync(x, d_x, (size_t)N * sizeof(T), cudaMemcpyDeviceToHost, st));
     if (reports_on_host) {
         unsigned char* h = single_rep_.template as<unsigned char>();
@@ -698,6 +729,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
         *iters = *reinterpret_cast<uint32_t*>(h + 8);
     } else {
         SSB_CUDA(cudaStreamSynchronize(st));
+    }
     }
     L.counters[3] += reports_on_host ? *iters : 0;
     merge(L);

@@ -35,8 +35,11 @@ template <typename T>
 struct SingleArgs {
     int N, Npad, Mp, Kmax, ks;
     const T* At; const T* G; int ldg;
-    const T* y;           // [Mp] zero padded signal
+    const T* y;           // [Mp] zero padded signal; may be PINNED HOST memory (read once, at the start)
+    T* ywork;             // [Mp] device copy of y for the exact mode's r = y - A_G x_G when y is host memory (else nullptr)
     T* x;                 // [N] output (zeroed by the kernel)
+    T* x_out;             // [N] pinned host copy of the finished x, written by the kernel (else nullptr): a host-pointer call is then
+                          //     one launch and one stream synchronise -- no staged copies
     T* P;                 // [Mp] scratch: current right-hand side
     T* R;                 // [Mp] scratch: current residual (exact mode)
     int exact;
@@ -47,6 +50,11 @@ struct SingleArgs {
     int cnt;              // atoms per CTA
     int dict_smem;        // 1: every CTA keeps its slice of the dictionary (cnt x Mp) in shared memory for the whole launch
     int stage;            // 1: SINGLE_STAGE_BYTES of shared memory are there for the gather of p = A_G d
+    // Gram iterations, as in the lockstep loop (homotopy_impl.cuh: solve_chunk): on iterations it < gram_iters (K <= it) every CTA forms
+    // q = G[:, active] d -- and, in exact mode, c' = A^T y - G[:, active] x -- over its slice from K rows of G = A^T A; no p, no r, no
+    // pass over the dictionary.  0 for coherent dictionaries; not used in resume mode.
+    uint32_t gram_iters;
+    uint32_t* pub_gam; T* pub_d; T* pub_x;   // grid form: CTA 0 publishes the active set, its direction and x on it here ([Kmax + 2] each)
     // ---- resume mode: the finisher of the lockstep loop.  The last few still-running signals of a chunk (stragglers that go on
     // to max_iterations long after the rest has converged) are taken from their lockstep state to the end here, one after the
     // other: an iteration then costs grid barriers instead of two thin launches and a host round trip.
@@ -66,7 +74,7 @@ constexpr int SINGLE_STAGE_BYTES = 16 * 1024;   // cluster form: the atom rows o
 template <typename T>
 inline size_t homotopy_single_smem(int Mp, int cnt, int Kmax, int ks, bool dict_slice = false, bool stage = false) {
     const size_t KC = (size_t)((Kmax + 2) & ~1);
-    return (2 * (size_t)Mp + 3 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64 +
+    return (2 * (size_t)Mp + 4 * (size_t)cnt + (size_t)(Kmax + 1) * ks + 6 * KC + 8) * sizeof(T) + ((size_t)cnt + KC) * sizeof(uint32_t) + 64 +
            (stage ? SINGLE_STAGE_BYTES + 16 : 0) + (dict_slice ? (size_t)cnt * Mp * sizeof(T) + 16 : 0);
 }
 
@@ -97,7 +105,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     T* s_c = s_r + a.Mp;                              // [cnt]
     T* s_q = s_c + a.cnt;                             // [cnt]
     T* s_c2 = s_q + a.cnt;                            // [cnt]  cluster form: the updated c goes here, then the two swap
-    T* s_G = s_c2 + a.cnt;                            // [(Kmax+1) * ks]   CTA 0 only from here on
+    T* s_c0 = s_c2 + a.cnt;                           // [cnt]  A^T y over the slice (exact mode, Gram iterations)
+    T* s_G = s_c0 + a.cnt;                            // [(Kmax+1) * ks]   CTA 0 only from here on (the others use s_gam / s_d / s_x as copies)
     T* s_d = s_G + (size_t)(a.Kmax + 1) * a.ks;
     T* s_u1 = s_d + KC;
     T* s_u2 = s_u1 + KC;
@@ -267,7 +276,8 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     for (int si = cid; si < nsig; si += ncl) {
     const int s = a.resume ? (a.act ? a.act[si] : si) : 0;
     T* xrow = a.resume ? a.X + (size_t)s * a.ldx : a.x;
-    const T* yrow = a.resume ? a.Y + (size_t)s * a.ldy : a.y;
+    const T* ysrc = a.resume ? a.Y + (size_t)s * a.ldy : a.y;
+    const T* yrow = (!a.resume && a.ywork) ? a.ywork : ysrc;
     const int ylen = a.resume ? a.M : a.Mp;          // a.y is zero padded to Mp, a caller's row is not
     uint32_t* it_out = a.resume ? a.itersv + s : a.iters;
     double* err_out = a.resume ? a.errsv + s : a.errs;
@@ -353,7 +363,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     };
     if (!a.resume) {
         // ---- initial state (homotopy-cpu.cpp:201-229)
-        for (int m = tid; m < a.Mp; m += THREADS) s_p[m] = yrow[m];
+        for (int m = tid; m < a.Mp; m += THREADS) { const T v = ysrc[m]; s_p[m] = v; if (cta == 0 && a.ywork) a.ywork[m] = v; }
         for (int n = a0 + tid; n < a1; n += THREADS) { s_act[n - a0] = 0u; if (n < a.N) xrow[n] = T(0); }
         __syncthreads();
         correlate(s_p);
@@ -363,6 +373,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             uint32_t bidx = 0xffffffffu;
             for (int n = a0 + tid; n < a1; n += THREADS) {
                 s_c[n - a0] = s_q[n - a0];
+                s_c0[n - a0] = s_q[n - a0];
                 if (n < a.N) { const T av = fabs(s_q[n - a0]); if (av > best) { best = av; bidx = (uint32_t)n; } }
             }
             warp_argmax_first(best, bidx);
@@ -396,6 +407,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     const T nrm = sqrt(a.G[(size_t)bidx * a.ldg + bidx]);       // online_inverse.h:193-201
                     const T inv = T(1) / (nrm * nrm);
                     s_gam[0] = bidx; s_G[0] = inv; s_d[0] = sign_tol(best, a.tol) * inv; s_x[0] = T(0);   // sign of |c|: :223-224
+                    if constexpr (!CLUSTER) { if (a.gram_iters > 1) { a.pub_gam[0] = bidx; a.pub_d[0] = s_d[0]; a.pub_x[0] = T(0); } }
                 }
                 __syncthreads();
                 const T d0 = s_d[0];
@@ -430,6 +442,38 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     for (;;) {
         ++it;
         SSB_PROF(14);
+        const bool gram = !a.resume && it < a.gram_iters;             // K <= it < gram_iters <= 32
+        const bool gram_next = !a.resume && it + 1 < a.gram_iters;    // the next iteration needs no right-hand side
+        if (gram) {
+            // the active set, its direction and (exact mode) x on it: from CTA 0
+            if (cta != 0) {
+                if constexpr (CLUSTER) {
+                    cg::cluster_group cl = cg::this_cluster();
+                    const uint32_t* rg = cl.map_shared_rank(s_gam, 0);
+                    const T* rd = cl.map_shared_rank(s_d, 0);
+                    const T* rx = cl.map_shared_rank(s_x, 0);
+                    if (tid < K) { s_gam[tid] = rg[tid]; s_d[tid] = rd[tid]; s_x[tid] = rx[tid]; }
+                } else {
+                    if (tid < K) { s_gam[tid] = __ldcg(a.pub_gam + tid); s_d[tid] = __ldcg(a.pub_d + tid); s_x[tid] = __ldcg(a.pub_x + tid); }
+                }
+            }
+            __syncthreads();
+            SSB_PROF(0);
+            // one thread per atom of the slice, slots in order (the sums of homotopy_scan_kernel's Gram form)
+            for (int n = a0 + tid; n < a1; n += THREADS) {
+                T qn = T(0), cn = s_c0[n - a0];
+                for (int k = 0; k < K; k += 16) {     // K <= 15 on the default 16 Gram iterations: every row in flight at once
+                    T gv[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) if (k + u < K) gv[u] = __ldg(a.G + (size_t)s_gam[k + u] * a.ldg + n);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) if (k + u < K) { qn += gv[u] * s_d[k + u]; cn -= gv[u] * s_x[k + u]; }
+                }
+                s_q[n - a0] = qn;
+                if (a.exact) s_c[n - a0] = cn;
+            }
+            __syncthreads();
+        } else {
         if constexpr (CLUSTER) {
             if (cta != 0) {
                 cg::cluster_group cl = cg::this_cluster();
@@ -444,6 +488,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         SSB_PROF(0);
         if (a.exact) correlate2(); else correlate(s_p);
         __syncthreads();
+        }
         SSB_PROF(1);
         if (a.exact) {   // lambda = |c'|_inf over the re-formed correlations (:270 on :255's c)
             T mx0 = T(0);
@@ -461,19 +506,29 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         // min-gamma search (:122-163): join candidates of the slice, leave candidates in CTA 0
         T best = TMAX;
         uint32_t bidx = 0xffffffffu;
-        for (int n = a0 + tid; n < a1 && n < a.N; n += THREADS) {
-            if (s_act[n - a0]) continue;
-            const T cc = s_c[n - a0], qq = s_q[n - a0];
-            const T dl = T(1) - qq, dr = T(1) + qq;
-            if (dl != T(0)) { const T t = (lam - cc) / dl; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
-            if (dr != T(0)) { const T t = (lam + cc) / dr; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
-        }
-        if (cta == 0)
-            for (int k = tid; k < K; k += THREADS) {
-                const T t = -s_x[k] / s_d[k];
-                if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
+        // a slice of <= 64 atoms (8 per CTA as a grid, 64 as a 16-cluster at N = 1024) is searched by warp 0 alone: one warp-level
+        // argmin and no block barrier; (value, index) is a total order, so the winner does not depend on who compares what
+        const bool small = a.cnt <= 64;
+        auto join_candidates = [&](int first, int stride) {
+            for (int n = a0 + first; n < a1 && n < a.N; n += stride) {
+                if (s_act[n - a0]) continue;
+                const T cc = s_c[n - a0], qq = s_q[n - a0];
+                const T dl = T(1) - qq, dr = T(1) + qq;
+                if (dl != T(0)) { const T t = (lam - cc) / dl; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
+                if (dr != T(0)) { const T t = (lam + cc) / dr; if (t > T(0) && t < TMAX && cand_less(t, (uint32_t)n, best, bidx & 0x7fffffffu)) { best = t; bidx = (uint32_t)n; } }
             }
-        block_argmin(best, bidx);
+            if (cta == 0)
+                for (int k = first; k < K; k += stride) {
+                    const T t = -s_x[k] / s_d[k];
+                    if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
+                }
+        };
+        if (small) {
+            if (warp == 0) { join_candidates(lane, 32); warp_argmin_flagged(best, bidx); }
+        } else {
+            join_candidates(tid, THREADS);
+            block_argmin(best, bidx);
+        }
         push_pair(best, bidx);
         if (cta == 0) push_index(G, s_act[0]);      // membership of atom 0, for the no-candidate case
         SSB_PROF(2);
@@ -496,19 +551,26 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         {
             T* const c_out = CLUSTER ? s_c2 : s_c;
             T mx = T(0);
-            for (int n = a0 + tid; n < a1; n += THREADS) {
-                const T cn = s_c[n - a0] - gamma * s_q[n - a0];
-                c_out[n - a0] = cn;
-                if constexpr (!CLUSTER) a.Cg[n] = cn;
-                if (n < a.N) mx = max(mx, fabs(cn));
-            }
+            auto step_c = [&](int first, int stride) {
+                for (int n = a0 + first; n < a1; n += stride) {
+                    const T cn = s_c[n - a0] - gamma * s_q[n - a0];
+                    c_out[n - a0] = cn;
+                    if constexpr (!CLUSTER) a.Cg[n] = cn;
+                    if (n < a.N) mx = max(mx, fabs(cn));
+                }
+            };
             if ((int)idx >= a0 && (int)idx < a1 && tid == 0) s_act[idx - a0] ^= 1u;
-            mx = warp_max(mx);
-            if (lane == 0) red_v[warp] = mx;
-            __syncthreads();
-            T m = red_v[0];
-            for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
-            push_max(m, false);
+            if (small) {
+                if (warp == 0) { step_c(lane, 32); push_max(warp_max(mx), false); }
+            } else {
+                step_c(tid, THREADS);
+                mx = warp_max(mx);
+                if (lane == 0) red_v[warp] = mx;
+                __syncthreads();
+                T m = red_v[0];
+                for (int w = 1; w < NW; ++w) m = max(m, red_v[w]);
+                push_max(m, false);
+            }
         }
         SSB_PROF(5);
 
@@ -593,7 +655,10 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
             matvec<T, THREADS, true>(s_G, ldm, Knew, s_cg, s_d, nullptr);
             __syncthreads();
             SSB_PROF(10);
-            if (publish) publish_rhs(Knew);
+            if (publish && !gram_next) publish_rhs(Knew);
+            if constexpr (!CLUSTER) {
+                if (gram_next) for (int k = tid; k < Knew; k += THREADS) { a.pub_gam[k] = s_gam[k]; a.pub_d[k] = s_d[k]; a.pub_x[k] = s_x[k]; }
+            }
         };
 
         T lam_new;
@@ -632,7 +697,9 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     }
     // scratch and shared memory are reused by the next signal; in cluster mode nobody may leave (or move on) while CTA 0 still reads
     // the others' shared memory
-    if (CLUSTER || si + 1 < nsig) sync_all();
+    if (CLUSTER || si + 1 < nsig || a.x_out) sync_all();
+    if (!a.resume && a.x_out)
+        for (int n = a0 + tid; n < a1 && n < a.N; n += THREADS) a.x_out[n] = __ldcg(xrow + n);
     }
 }
 

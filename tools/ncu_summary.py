@@ -80,5 +80,5 @@ for pat in sorted(set(n.split("(")[0].split("<")[0].split("::")[-1].split()[-1] 
     tot = sum(d[0] for d in data) or 1
     print(f"\n== stall samples, kernel ~{pat}: total {tot} (first launch)")
     print("   by reason:", ", ".join(f"{k[6:]} {100 * v / tot:.1f}%" for k, v in sorted(tot_by.items(), key=lambda kv: -kv[1])[:8]))
-    for n, sass, r in sorted(data, key=lambda d: -d[0])[:14]:
+    for n, sass, r in sorted(data, key=lambda d: -d[0])[:int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 14]:
         print(f"   {100 * n / tot:5.1f}%  {sass[:100]}")
