@@ -372,13 +372,13 @@ int ssb200_homotopy_get_residual_info(void* h, int* mode_in_effect, double* cohe
                        if (coherence) *coherence = mu; }); }
 #if SSB_SINGLE_PROF
 // variant builds only (tools/single_prof.py): the phase timer of the single-signal kernel, read and cleared
-int ssb200_debug_single_profile(uint64_t out[16])
+int ssb200_debug_single_profile(uint64_t out[32])
 {
     return guarded([&] {
-        unsigned long long h[16], z[16] = {};
+        unsigned long long h[32], z[32] = {};
         SSB_CUDA(cudaMemcpyFromSymbol(h, g_single_prof, sizeof(h)));
         SSB_CUDA(cudaMemcpyToSymbol(g_single_prof, z, sizeof(z)));
-        for (int i = 0; i < 16; ++i) out[i] = h[i];
+        for (int i = 0; i < 32; ++i) out[i] = h[i];
     });
 }
 #endif

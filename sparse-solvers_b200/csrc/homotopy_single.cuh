@@ -25,8 +25,10 @@ namespace ssb {
 #define SSB_SINGLE_PROF 0
 #endif
 #if SSB_SINGLE_PROF
-__device__ unsigned long long g_single_prof[16];
-#define SSB_PROF(i) do { if (threadIdx.x == 0 && cta == 0) { const long long t_ = clock64(); g_single_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = t_; } } while (0)
+__device__ unsigned long long g_single_prof[32];
+// (sums are kept in shared memory and flushed when the solve ends: a read-modify-write of global memory per probe stalls warp 0 for
+// an L2 round trip, which is what the first version of this timer mostly measured)
+#define SSB_PROF(i) do { if (threadIdx.x == 0 && cta == 0) { const long long t_ = clock64(); s_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = t_; } } while (0)
 #else
 #define SSB_PROF(i) do {} while (0)
 #endif
@@ -86,7 +88,7 @@ constexpr int SINGLE_CLUSTER_MAX = 16;   // CTAs of a cluster (16 needs the non-
 //                  sides are read from CTA 0's shared memory and c at the active atoms from its owner's (distributed shared memory):
 //                  no global scratch, no fence.  Same arithmetic, same order: results are the same bits.
 template <typename T, int THREADS, bool CLUSTER>
-__global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> a)
+__global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<T> a)
 {
     namespace cg = cooperative_groups;
     constexpr int V = 16 / sizeof(T);
@@ -261,7 +263,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         if constexpr (CLUSTER) {
             v = lane < G ? xp_t[lane] : TMAX;
             i = lane < G ? xp_i[lane] : 0xffffffffu;
-            warp_argmin_flagged(v, i);
+            warp_argmin_flagged_fast(v, i);
         } else {
             v = TMAX; i = 0xffffffffu;
             for (int g = tid; g < G; g += THREADS) {
@@ -438,6 +440,11 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
     sync_all();
 
     // ---- the loop (homotopy-cpu.cpp:236-272)
+#if SSB_SINGLE_PROF
+    __shared__ unsigned long long s_prof[32];
+    if (threadIdx.x < 32) s_prof[threadIdx.x] = 0;
+    __syncthreads();
+#endif
     [[maybe_unused]] long long prof_t = clock64();
     for (;;) {
         ++it;
@@ -466,12 +473,18 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     T gv[16];
 #pragma unroll
                     for (int u = 0; u < 16; ++u) if (k + u < K) gv[u] = __ldg(a.G + (size_t)s_gam[k + u] * a.ldg + n);
+                    if (a.exact) {
 #pragma unroll
-                    for (int u = 0; u < 16; ++u) if (k + u < K) { qn += gv[u] * s_d[k + u]; cn -= gv[u] * s_x[k + u]; }
+                        for (int u = 0; u < 16; ++u) if (k + u < K) { qn += gv[u] * s_d[k + u]; cn -= gv[u] * s_x[k + u]; }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) if (k + u < K) qn += gv[u] * s_d[k + u];
+                    }
                 }
                 s_q[n - a0] = qn;
                 if (a.exact) s_c[n - a0] = cn;
             }
+            SSB_PROF(23);
             __syncthreads();
         } else {
         if constexpr (CLUSTER) {
@@ -524,12 +537,45 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                 }
         };
         if (small) {
-            if (warp == 0) { join_candidates(lane, 32); warp_argmin_flagged(best, bidx); }
+            if (warp == 0) {
+                // <= 2 atoms and <= 1 active slot per lane (more slots: the loop): every quotient is formed first, side by side, then
+                // they are compared in the order of join_candidates
+                T tl[2], tr[2], tx = T(0);
+                bool live[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int n = a0 + lane + 32 * u;
+                    live[u] = n < a1 && n < a.N && !s_act[min(n, a1 - 1) - a0];
+                    const T cc = live[u] ? s_c[n - a0] : T(0), qq = live[u] ? s_q[n - a0] : T(0);
+                    tl[u] = (lam - cc) / (T(1) - qq);
+                    tr[u] = (lam + cc) / (T(1) + qq);
+                }
+                const bool leave = cta == 0 && lane < K;
+                if (leave) tx = -s_x[lane] / s_d[lane];
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+                    if (live[u]) {
+                        const uint32_t n = (uint32_t)(a0 + lane + 32 * u);
+                        const T qq = s_q[n - a0];
+                        if (T(1) - qq != T(0) && tl[u] > T(0) && tl[u] < TMAX && cand_less(tl[u], n, best, bidx & 0x7fffffffu)) { best = tl[u]; bidx = n; }
+                        if (T(1) + qq != T(0) && tr[u] > T(0) && tr[u] < TMAX && cand_less(tr[u], n, best, bidx & 0x7fffffffu)) { best = tr[u]; bidx = n; }
+                    }
+                if (leave && tx > T(0) && tx < TMAX && cand_less(tx, s_gam[lane], best, bidx & 0x7fffffffu)) { best = tx; bidx = s_gam[lane] | 0x80000000u; }
+                if (cta == 0)
+                    for (int k = lane + 32; k < K; k += 32) {
+                        const T t = -s_x[k] / s_d[k];
+                        if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
+                    }
+                SSB_PROF(16);
+                warp_argmin_flagged_fast(best, bidx);
+                SSB_PROF(17);
+            }
         } else {
             join_candidates(tid, THREADS);
             block_argmin(best, bidx);
         }
         push_pair(best, bidx);
+        SSB_PROF(18);
         if (cta == 0) push_index(G, s_act[0]);      // membership of atom 0, for the no-candidate case
         SSB_PROF(2);
         sync_all();
@@ -606,12 +652,15 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                 for (int k = tid + THREADS; k < K; k += THREADS) s_u1[k] = a.G[(size_t)idx * a.ldg + s_gam[k]];
                 const T dot = pre_dot;
                 __syncthreads();
+                SSB_PROF(19);
                 matvec<T, THREADS, true>(s_G, ldm, K, s_u1, s_u2, nullptr);
                 __syncthreads();
+                SSB_PROF(20);
                 T uu = T(0);
                 for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
                 uu = warp_sum(uu);
                 const T dd = T(1) / (dot - uu);
+                SSB_PROF(21);
                 for (int e = tid; e < K * K; e += THREADS) {
                     const int r = e / K, k = e - r * K;
                     s_G[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
@@ -622,6 +671,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
                     s_G[(size_t)K * ldm + r] = u3;
                 }
                 if (tid == 0) { s_G[(size_t)K * ldm + K] = dd; s_gam[K] = idx; s_x[K] = pre_x; }
+                SSB_PROF(22);
             } else {
                 // online_inverse.h:253-293; the leaving atom sits in slot j
                 const int j = slot;
@@ -692,9 +742,13 @@ __global__ void __launch_bounds__(THREADS) homotopy_single_kernel(SingleArgs<T> 
         if (!cont) break;
         if constexpr (!CLUSTER) { sync_all(); SSB_PROF(12); }
 #if SSB_SINGLE_PROF
-        if (tid == 0 && cta == 0) g_single_prof[15] += 1;
+        if (tid == 0 && cta == 0) s_prof[15] += 1;
 #endif
     }
+#if SSB_SINGLE_PROF
+    __syncthreads();
+    if (cta == 0 && threadIdx.x < 32) atomicAdd(&g_single_prof[threadIdx.x], s_prof[threadIdx.x]);
+#endif
     // scratch and shared memory are reused by the next signal; in cluster mode nobody may leave (or move on) while CTA 0 still reads
     // the others' shared memory
     if (CLUSTER || si + 1 < nsig || a.x_out) sync_all();

@@ -29,6 +29,19 @@ __device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
     }
 }
 
+// the same result from three warp-wide integer reductions (REDUX) instead of five rounds of two shuffles and a compare: a float
+// candidate is strictly positive (or the FLT_MAX sentinel), so its bits order like its value; ties go to the lowest index, and the
+// one lane that holds the winner hands out its flag.  float64 keeps the shuffle form.
+__device__ __forceinline__ void warp_argmin_flagged_fast(float& v, uint32_t& i) {
+    const uint32_t kv = __float_as_uint(v);
+    const uint32_t mv = __reduce_min_sync(0xffffffffu, kv);
+    const uint32_t mi = __reduce_min_sync(0xffffffffu, kv == mv ? (i & 0x7fffffffu) : 0xffffffffu);
+    const bool mine = kv == mv && (i & 0x7fffffffu) == mi;
+    i = __reduce_max_sync(0xffffffffu, mine ? i : 0u);
+    v = __uint_as_float(mv);
+}
+__device__ __forceinline__ void warp_argmin_flagged_fast(double& v, uint32_t& i) { warp_argmin_flagged(v, i); }
+
 // The kernel is bound by the dependent round trips of one CTA times the CTAs an SM holds, so everything is fetched in
 // two: position -> signal, then c, q, the membership bits of this thread's atoms (a per-signal bitmask kept in HBM by
 // the algebra kernel), K, lambda and -- speculatively, for every slot below the iteration's bound kb -- the active set

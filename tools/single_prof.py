@@ -16,7 +16,7 @@ for b in range(8): s.solve(Y[b], 1e-3, mi)
 PH = ["p copy", "correlate", "search+argmin+push", "barrier 1", "partials+argmin", "c update+push", "barrier 2", "lambda", "x,slot,c_G gather",
       "inverse update", "direction", "rhs gather", "barrier 3"]
 have = hasattr(lib(), "ssb200_debug_single_profile")
-out = (C.c_uint64 * 16)()
+out = (C.c_uint64 * 32)()
 if have: lib().ssb200_debug_single_profile(out)
 s.set_timing(True); s.reset_counters()
 t0 = time.perf_counter(); its = []
@@ -34,3 +34,7 @@ if have:
     print(f"  cycles per loop iteration (CTA 0): total {tot / iters:.0f}")
     for i, name in enumerate(PH):
         print(f"    {name:22s} {out[i] / iters:8.0f}")
+    SUB = {16: "search: candidates", 17: "search: warp argmin", 18: "search: push", 19: "inverse: u1 + barrier", 20: "inverse: matvec", 21: "inverse: uu, 1/x",
+           22: "inverse: K x K update", 23: "gram q: loads + sums"}
+    for i, name in SUB.items():
+        print(f"      [{name:22s} {out[i] / iters:8.0f}]  (inside the phase that ends after it; a probe costs ~360)")
