@@ -655,10 +655,21 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     SSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     SSB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
     if (!coop) return false;
-    const int kmax = active_set_capacity(max_iter, N);
-    const int ks = (kmax + 1) | 1;
+    // Slots for the active set.  min(max_iterations + 1, N) can never overflow; a full-rank active set has at most M atoms, so when the
+    // host reads the report anyway the launch gets min(.., M + 1) slots -- the reference's bench passes max_iterations = N, which would
+    // otherwise keep every N >= 256 cell off this kernel -- and a solve that does ask for more (rank-deficient numerics, tiny
+    // tolerances) reports so and is solved again by the lockstep path.
+    int kmax = active_set_capacity(max_iter, N);
     const int grid = std::min(sms, (Npad + 7) / 8);
     const int cnt = (Npad + grid - 1) / grid;
+    if (reports_on_host && x_on_host) {
+        kmax = std::min(kmax, M + 1);
+        // ... and no more than the K x K inverse finds room for in shared memory (float32: ~210 slots): most solves of the reference's
+        // 256 x N bench cells stay below that, the others cost one abandoned launch
+        const int cnt_cluster = (Npad + SINGLE_CLUSTER_MAX - 1) / SINGLE_CLUSTER_MAX;
+        while (kmax > 48 && homotopy_single_smem<T>(Mp, std::max(cnt, cnt_cluster), kmax, (kmax + 1) | 1, false, true) > 200 * 1024) kmax -= 8;
+    }
+    const int ks = (kmax + 1) | 1;
     const size_t smem = homotopy_single_smem<T>(Mp, cnt, kmax, ks);
     if (smem > 200 * 1024) return false;
     static std::atomic<uint64_t> configured{ 0 };
@@ -716,6 +727,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
     L.counters[0]++;
     if (zero_copy) {
         SSB_CUDA(cudaStreamSynchronize(st));
+        if (*reinterpret_cast<uint32_t*>(hp + 8) == 0xffffffffu) { merge(L); return false; }   // out of slots: the lockstep path takes it
         std::memcpy(x, hp + 64 + (size_t)Mp * sizeof(T), (size_t)N * sizeof(T));
         *errs = *reinterpret_cast<double*>(hp);
         *iters = *reinterpret_cast<uint32_t*>(hp + 8);
@@ -725,6 +737,7 @@ bool Homotopy<T>::solve_single(const T* y, bool y_on_host, T tol, uint32_t max_i
         unsigned char* h = single_rep_.template as<unsigned char>();
         SSB_CUDA(cudaMemcpyAsync(h, d_err, 16, cudaMemcpyDeviceToHost, st));
         SSB_CUDA(cudaStreamSynchronize(st));
+        if (*reinterpret_cast<uint32_t*>(h + 8) == 0xffffffffu) { merge(L); return false; }
         *errs = *reinterpret_cast<double*>(h);
         *iters = *reinterpret_cast<uint32_t*>(h + 8);
     } else {

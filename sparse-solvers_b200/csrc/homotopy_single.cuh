@@ -592,6 +592,11 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
             if (cta == 0 && tid == 0) { *it_out = it; *err_out = (double)lam; }
             break;
         }
+        if (Knew > a.Kmax) {   // the host gave this launch fewer slots than min(max_iterations + 1, N) (a full-rank active set has at most
+                               // M atoms): nothing has been written for this iteration; the caller solves again on the lockstep path
+            if (cta == 0 && tid == 0) { *it_out = 0xffffffffu; *err_out = (double)lam; }
+            break;
+        }
         // c -= gamma q on the slice, |c|_inf partial (:255, :270).  Cluster form: into the slice's second buffer, so that CTA 0 can form
         // c at the active atoms itself from the owners' old c and q while they are still at it -- no barrier before the algebra
         {

@@ -130,6 +130,28 @@ def test_single_solve_cluster_form_equals_the_grid_form(ss, dtype, shape, k, max
     assert max(r.iter for _, r in got["grid"]) == max_iter
 
 
+def test_single_solve_out_of_slots_falls_back_to_the_lockstep_path(ss):
+    """The single-signal kernel is launched with min(max_iterations + 1, N, M + 1) active-set slots (a full-rank active set has at
+    most M atoms; the reference's bench passes max_iterations = N).  A solve that asks for more -- here: tolerance ~0, so it keeps
+    adding atoms past K = M on rounding residue -- reports so, and the call is answered by the lockstep path instead: the same
+    result as that path gives for the signal inside a batch."""
+    rng = np.random.default_rng(5)
+    A = rng.standard_normal((8, 64))
+    A /= np.linalg.norm(A, axis=0)
+    y = rng.standard_normal(8)
+    s = ss.Homotopy(A)
+    s.reset_counters()
+    x, rep = s.solve(y, 1e-300, 40)
+    assert s.counters()["launches"] > 3, "the fall-back did not run"
+    Xb, itb, eb = s.solve_batch(np.stack([y, y]), 1e-300, 40)
+    assert rep.iter == itb[0] and rep.iter > 9
+    np.testing.assert_array_equal(x, Xb[0])
+    # and a solve that stays within M + 1 slots is served by the single kernel: one launch
+    s.reset_counters()
+    x2, rep2 = s.solve(y, 1e-3, 40)
+    assert s.counters()["launches"] == 1 and rep2.iter <= 12
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_smoke_identity(ss, dtype):
     """test_util.h:27-55, test_binding.py:9-20: x == signal exactly, iter == 1, solution_error == 0."""
