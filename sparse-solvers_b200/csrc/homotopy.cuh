@@ -354,7 +354,7 @@ private:
     bool solve_single(const T* y, bool y_on_host, T tol, uint32_t max_iter, T* x, bool x_on_host, uint32_t* iters, double* errs,
                       bool reports_on_host);
     // the same kernel as thread-block clusters (one cluster per signal, `nclusters` signals at a time): fills a.cnt and launches on
-    // `st`; false = does not apply (dictionary too large to stream through one cluster, device refuses the cluster, SSB200_CLUSTER=0)
+    // `st`; false = does not apply (dictionary too large to stream through one cluster, device refuses the cluster, SSB200_SINGLE_CLUSTER=0)
     bool launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStream_t st);
     dev_buffer single_ws_;
     pinned_buffer single_rep_, single_pin_;

@@ -551,7 +551,7 @@ void Homotopy<T>::run_lanes(int nlanes, size_t nchunks, F&& body)
 template <typename T>
 bool Homotopy<T>::launch_single_cluster(SingleArgs<T>& a, int nclusters, cudaStream_t st)
 {
-    if (const char* e = getenv("SSB200_CLUSTER")) if (atoi(e) == 0) return false;                      // tuning knob / A-B switch
+    if (const char* e = getenv("SSB200_SINGLE_CLUSTER")) if (atoi(e) == 0) return false;                      // tuning knob / A-B switch
     if ((size_t)Npad * Mp * sizeof(T) > ((size_t)8 << 20)) return false;
     constexpr int THREADS = 256;
     auto fn = homotopy_single_kernel<T, THREADS, true>;

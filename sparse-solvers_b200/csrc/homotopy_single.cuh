@@ -532,7 +532,7 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
             }
             if (cta == 0)
                 for (int k = first; k < K; k += stride) {
-                    const T t = -s_x[k] / s_d[k];
+                    const T xk_ = s_x[k]; const T t = xk_ == T(0) ? T(0) : -xk_ / s_d[k];   // x = 0 (the atom that just joined) is no candidate either way: skip the division's slow path
                     if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
                 }
         };
@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
                     tr[u] = (lam + cc) / (T(1) + qq);
                 }
                 const bool leave = cta == 0 && lane < K;
-                if (leave) tx = -s_x[lane] / s_d[lane];
+                if (leave && s_x[lane] != T(0)) tx = -s_x[lane] / s_d[lane];   // x = 0 (the atom that just joined): no candidate, and a zero numerator takes the division's slow path
 #pragma unroll
                 for (int u = 0; u < 2; ++u)
                     if (live[u]) {
@@ -563,7 +563,7 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
                 if (leave && tx > T(0) && tx < TMAX && cand_less(tx, s_gam[lane], best, bidx & 0x7fffffffu)) { best = tx; bidx = s_gam[lane] | 0x80000000u; }
                 if (cta == 0)
                     for (int k = lane + 32; k < K; k += 32) {
-                        const T t = -s_x[k] / s_d[k];
+                        const T xk_ = s_x[k]; const T t = xk_ == T(0) ? T(0) : -xk_ / s_d[k];   // x = 0 (the atom that just joined) is no candidate either way: skip the division's slow path
                         if (t > T(0) && t < TMAX && cand_less(t, s_gam[k], best, bidx & 0x7fffffffu)) { best = t; bidx = s_gam[k] | 0x80000000u; }
                     }
                 SSB_PROF(16);

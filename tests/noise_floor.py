@@ -8,7 +8,8 @@
 For every configuration the same seeded inputs go to
   ref   the UNMODIFIED reference (oracle/_ref, OpenBLAS through the reference's own dlopen)
   port  the plain-C restatement (oracle/ss_oracle.c)
-  gpu   libssb200.so through the C ABI, in the residual modes asked for (auto / exact / incremental)
+  gpu   libssb200.so through the C ABI, in the residual modes asked for (auto / exact / incremental: the batched lockstep path;
+        single / single-exact: one call per signal, i.e. the single-signal cluster kernel)
 and the pairs (port, ref) = CPU-against-CPU noise floor, (gpu, ref), (gpu, port) are compared with tests/parity.py:
 iter = iteration-count mismatches, support = hard support mismatches, soft = support flips of rounding residue,
 coef_1e-4 / coef_1e-3 = signals whose largest coefficient error relative to max|x_ref| exceeds that, err = solution_error
@@ -121,7 +122,8 @@ def main():
     ap.add_argument("--gpu", action="store_true")
     ap.add_argument("--merge", default=None)
     ap.add_argument("--tag", default="default", help="names this library build in the record (e.g. ieee-order)")
-    ap.add_argument("--modes", default="auto,exact,incremental")
+    ap.add_argument("--modes", default="auto,exact,incremental,single,single-exact",
+                    help="residual modes of the batched path; single / single-exact = one ssb200_homotopy_solve call per signal")
     ap.add_argument("--only", default=None, help="substring filter on the configuration names")
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
@@ -153,10 +155,20 @@ def main():
             solver = ss.Homotopy(A)
             out = {}
             for mode in args.modes.split(","):
-                solver.set_residual_mode(mode)
+                single = mode.startswith("single")
+                solver.set_residual_mode({"single": "auto", "single-exact": "exact"}.get(mode, mode))
                 eff, mu = solver.residual_info()
                 t0 = time.time()
-                g = solver.solve_batch(Y, cfg["tol"], cfg["max_iter"])
+                if single:      # one call per signal: the single-signal kernel (thread-block cluster form)
+                    if A.shape[0] * A.shape[1] > (1 << 21):
+                        continue
+                    X = np.empty((len(Y), A.shape[1]), dtype=A.dtype); it = np.empty(len(Y), dtype=np.uint32); er = np.empty(len(Y))
+                    for b in range(len(Y)):
+                        X[b], rep = solver.solve(Y[b], cfg["tol"], cfg["max_iter"])
+                        it[b], er[b] = rep.iter, rep.solution_error
+                    g = (X, it, er)
+                else:
+                    g = solver.solve_batch(Y, cfg["tol"], cfg["max_iter"])
                 mi_q = cfg["max_iter"] if name.startswith("quirk") else None
                 out[mode] = {"mode_in_effect": eff, "coherence": round(mu, 4), "gpu_vs_ref": compare(g, r, c0, mi_q), "gpu_vs_port": compare(g, p, c0, mi_q),
                              "seconds": round(time.time() - t0, 2), "gpu_mean_iters": float(g[1].mean()),

@@ -118,7 +118,7 @@ def test_single_solve_cluster_form_equals_the_grid_form(ss, dtype, shape, k, max
     s = ss.Homotopy(A)
     s.set_residual_mode(mode)
     got = {}
-    for form, env in (("grid", {"SSB200_CLUSTER": "0"}), ("cluster16", {"SSB200_CLUSTER": "1"}), ("cluster8", {"SSB200_CLUSTER": "1", "SSB200_CLUSTER_SIZE": "8"})):
+    for form, env in (("grid", {"SSB200_SINGLE_CLUSTER": "0"}), ("cluster16", {"SSB200_SINGLE_CLUSTER": "1"}), ("cluster8", {"SSB200_SINGLE_CLUSTER": "1", "SSB200_CLUSTER_SIZE": "8"})):
         monkeypatch.delenv("SSB200_CLUSTER_SIZE", raising=False)
         for key, v in env.items():
             monkeypatch.setenv(key, v)

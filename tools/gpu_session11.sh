@@ -18,8 +18,8 @@ except Exception as e:
 P
 }
 c1() { local tag=$1; shift; env "$@" python bench.py --config C1 --no-cpu-baseline > $O/s11_c1_$tag.json 2> $O/s11_c1_$tag.err; brief $O/s11_c1_$tag.json "C1 $tag"; }
-c1 grid SSB200_CLUSTER=0
-c1 cluster16 SSB200_CLUSTER=1
+c1 grid SSB200_SINGLE_CLUSTER=0
+c1 cluster16 SSB200_SINGLE_CLUSTER=1
 c1 cluster16_nodict SSB200_CLUSTER_DICT=0
 c1 cluster8 SSB200_CLUSTER_SIZE=8
 c1 cluster4 SSB200_CLUSTER_SIZE=4
@@ -29,4 +29,4 @@ c2 kr1 A=1
 c2 kr3 SSB200_SCAN_KR3=1
 c2 kr1_again A=1
 c2 kr3_again SSB200_SCAN_KR3=1
-c2 kr1_nocluster SSB200_CLUSTER=0
+c2 kr1_nocluster SSB200_SINGLE_CLUSTER=0

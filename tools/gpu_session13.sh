@@ -5,10 +5,10 @@ timeout 900 python -m pytest tests/test_gpu_homotopy.py -m gpu -x -q -p no:cache
 V=$PWD/build/variants/prof/libssb200.so
 python tools/single_prof.py
 SSB200_CLUSTER_STAGE=0 python tools/single_prof.py
-SSB200_CLUSTER=0 python tools/single_prof.py
+SSB200_SINGLE_CLUSTER=0 python tools/single_prof.py
 SSB200_LIB=$V python tools/single_prof.py
-SSB200_LIB=$V SSB200_CLUSTER=0 python tools/single_prof.py
+SSB200_LIB=$V SSB200_SINGLE_CLUSTER=0 python tools/single_prof.py
 python tools/single_prof.py 512 2048 32 80
-SSB200_CLUSTER=0 python tools/single_prof.py 512 2048 32 80
+SSB200_SINGLE_CLUSTER=0 python tools/single_prof.py 512 2048 32 80
 python tools/single_prof.py 504 1216 40 100
-SSB200_CLUSTER=0 python tools/single_prof.py 504 1216 40 100
+SSB200_SINGLE_CLUSTER=0 python tools/single_prof.py 504 1216 40 100

@@ -31,10 +31,10 @@ if have:
     lib().ssb200_debug_single_profile(out)
     iters = max(1, out[15])
     tot = sum(out[i] for i in range(13))
-    print(f"  cycles per loop iteration (CTA 0): total {tot / iters:.0f}")
+    print(f"  cycles per loop iteration as thread 0 of CTA 0 sees them (a probe costs ~60): phases {tot / iters:.0f} + inner slots {sum(out[i] for i in range(16, 24)) / iters:.0f}")
     for i, name in enumerate(PH):
         print(f"    {name:22s} {out[i] / iters:8.0f}")
     SUB = {16: "search: candidates", 17: "search: warp argmin", 18: "search: push", 19: "inverse: u1 + barrier", 20: "inverse: matvec", 21: "inverse: uu, 1/x",
            22: "inverse: K x K update", 23: "gram q: loads + sums"}
     for i, name in SUB.items():
-        print(f"      [{name:22s} {out[i] / iters:8.0f}]  (inside the phase that ends after it; a probe costs ~360)")
+        print(f"      [{name:22s} {out[i] / iters:8.0f}]  (its own slot, not part of the phase it sits in)")
