@@ -687,12 +687,20 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
         uu = warp_sum(uu);
         const T dd = T(1) / (dot - uu);                                                       // :228
-        {                                                                                     // inv += d u2 u2^T
+        if (K >= 24) {                                                                        // inv += d u2 u2^T
+            // a warp per row, lanes along it: per element a load, a multiply-add and a store (the flat loop below pays an index
+            // split and two more loads per element -- ncu r2, C3: this kernel is issue-bound on exactly that pass); same
+            // expression per element, so the same bits
+            for (int r = warp; r < K; r += NW) {
+                const T t = dd * s_u2[r];
+                T* g = Gm + (size_t)r * ldm;
+                for (int k = lane; k < K; k += 32) g[k] += t * s_u2[k];
+            }
+        } else {
             // row = e / K by multiply-high, exact while e * K < 2^32, i.e. K < 1625; a plain division beyond
             const uint32_t total = (uint32_t)(K * K), magic = (uint32_t)((0x100000000ull + K - 1) / K);
-            const bool mulhi_exact = K < 1600;
             for (uint32_t e = tid; e < total; e += THREADS) {
-                const uint32_t r = mulhi_exact ? __umulhi(e, magic) : e / (uint32_t)K, k = e - r * K;
+                const uint32_t r = __umulhi(e, magic), k = e - r * K;
                 Gm[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
             }
         }

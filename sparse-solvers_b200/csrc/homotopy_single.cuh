@@ -666,9 +666,10 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
                 uu = warp_sum(uu);
                 const T dd = T(1) / (dot - uu);
                 SSB_PROF(21);
-                for (int e = tid; e < K * K; e += THREADS) {
-                    const int r = e / K, k = e - r * K;
-                    s_G[(size_t)r * ldm + k] += (dd * s_u2[r]) * s_u2[k];
+                for (int r = warp; r < K; r += NW) {          // a warp per row, lanes along it (no index split; the same expression)
+                    const T t = dd * s_u2[r];
+                    T* g = s_G + (size_t)r * ldm;
+                    for (int k = lane; k < K; k += 32) g[k] += t * s_u2[k];
                 }
                 for (int r = tid; r < K; r += THREADS) {
                     const T u3 = -dd * s_u2[r];
@@ -685,9 +686,11 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
                 __syncthreads();
                 for (int r = tid; r < K; r += THREADS) s_u1[r] = s_G[(size_t)r * ldm + j] * sc;
                 __syncthreads();
-                for (int e = tid; e < K * K; e += THREADS) {
-                    const int r = e / K, k = e - r * K;
-                    if (r != j && k != j) s_G[(size_t)r * ldm + k] += (-dd * s_u1[r]) * s_u1[k];
+                for (int r = warp; r < K; r += NW) {
+                    if (r == j) continue;
+                    const T t = -dd * s_u1[r];
+                    T* g = s_G + (size_t)r * ldm;
+                    for (int k = lane; k < K; k += 32) if (k != j) g[k] += t * s_u1[k];
                 }
                 __syncthreads();
                 const int last = K - 1;

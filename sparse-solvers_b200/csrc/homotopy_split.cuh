@@ -392,7 +392,20 @@ __global__ void __launch_bounds__(W * 32) homotopy_algebra_kernel(HomArgs<T> a, 
         for (int k = lane; k < K; k += 32) uu += s_u1[k] * s_u2[k];
         uu = warp_sum(uu);
         const T dd = T(1) / (dot - uu);                                                     // :228
-        {                                                                                   // inv += d u2 u2^T
+        if (K >= 24) {                                                                      // inv += d u2 u2^T
+            // row by row, lanes along the row, this lane's u2 entries in registers: a load, a multiply-add and a store per element
+            // (the flat loop below pays an index split and two more loads, but fills the lanes better while K is small)
+            T u2k[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) u2k[j] = lane + 32 * j < K ? s_u2[lane + 32 * j] : T(0);
+            for (int r = 0; r < K; ++r) {
+                const T t = dd * s_u2[r];
+                T* g = s_G + (size_t)r * ks;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) if (lane + 32 * j < K) g[lane + 32 * j] += t * u2k[j];
+                for (int k = lane + 128; k < K; k += 32) g[k] += t * s_u2[k];
+            }
+        } else {
             const uint32_t total = (uint32_t)(K * K), magic = (uint32_t)((0x100000000ull + K - 1) / K);
             for (uint32_t e = lane; e < total; e += 32) {
                 const uint32_t r = __umulhi(e, magic), k = e - r * K;
