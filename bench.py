@@ -382,6 +382,19 @@ def run_single(args, cfg):
             t1 = time.perf_counter(); Xr, itr, er = ref.homotopy(A, Y[:sample], cfg["tol"], cfg["max_iter"], threads=1); dt = time.perf_counter() - t1
             cpu = {"value": sample / dt, "unit": "signals/s", "cores": 1, "kind": "reference",
                    "sample": f"first {sample} signals, one call at a time, 1 thread, {dt:.2f} s", "iters_match_gpu": int((itr == its[:sample]).sum())}
+    # the same calls through the reference's own pybind11 module linked on libssb200 (dropin/): what a user of the reference sees after
+    # swapping the library -- includes the stub's per-solve check that the dictionary view has not been edited
+    dropin = None
+    mod = os.path.join(ROOT, "dropin", "_build", "sparsesolvers")
+    if os.path.isdir(mod):
+        import subprocess
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "dropin", "time_c1.py"), str(cfg["m"]), str(cfg["n"]), str(cfg["k"]), str(cfg["tol"]),
+                            str(cfg["max_iter"]), str(batch), str(max(1, args.steps // 4))], capture_output=True, text=True, timeout=900)
+        try:
+            dropin = json.loads(r.stdout.strip().splitlines()[-1])
+            dropin["through"] = "the reference's unchanged binding.cpp + headers, Policy::run -> ssb200_homotopy_solve_f32 (dropin/ss_b200_policies.cpp)"
+        except Exception:
+            dropin = {"error": (r.stderr or r.stdout)[-300:]}
     line = {"metric": "homotopy signals/sec (single-signal calls)", "value": value, "unit": "signals/s", "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
@@ -391,8 +404,8 @@ def run_single(args, cfg):
             "gpu_launches": solver.counters()["launches"],
             "roofline": {"kernel": "homotopy_single_kernel", "bound": "hbm", "achieved": nbytes / secs / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": nbytes / secs / 1e9 / peaks["hbm_gbs"], "traffic": None,
-                         "note": "A (1 MB) is L2-resident: the bound that bites is three grid barriers + call overhead per iteration, not bandwidth"},
-            "cpu_baseline": cpu}
+                         "note": "A (1 MB) is L2-resident: what bounds this path is the latency chain of an iteration (two cluster barriers, one L2 and two DSMEM round trips, the K x K algebra in one CTA) + call overhead, not bandwidth"},
+            "dropin": dropin, "cpu_baseline": cpu}
     emit(line)
 
 

