@@ -308,10 +308,10 @@ private:
     void apply_l2_policy(cudaStream_t st);
 
     struct plan_key {
-        size_t batch; int kmax; bool host_path; int env_lanes, env_chunk; bool exact;
+        size_t batch; int kmax; bool host_path; int env_lanes, env_chunk; bool exact, timing;
         bool operator==(const plan_key& o) const {
             return batch == o.batch && kmax == o.kmax && host_path == o.host_path && env_lanes == o.env_lanes && env_chunk == o.env_chunk &&
-                   exact == o.exact;
+                   exact == o.exact && timing == o.timing;
         }
     };
     plan_key plan_key_{};

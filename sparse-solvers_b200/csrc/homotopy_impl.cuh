@@ -68,7 +68,7 @@ void Homotopy<T>::plan_batch(size_t batch, int kmax, bool host_path, size_t& chu
     // the plan of the previous call with the same shape is reused: cudaMemGetInfo goes through the resource manager and was
     // measured to take 10-80 ms every few calls on a busy box (tools/variance.py: the only slow part of a slow step)
     const char* env_l = getenv("SSB200_LANES"); const char* env_c = getenv("SSB200_CHUNK");
-    const plan_key key{ batch, kmax, host_path, env_l ? atoi(env_l) : -1, env_c ? atoi(env_c) : -1, exact_residual() };
+    const plan_key key{ batch, kmax, host_path, env_l ? atoi(env_l) : -1, env_c ? atoi(env_c) : -1, exact_residual(), timing };
     if (plan_valid_ && key == plan_key_) { chunk = plan_chunk_; nlanes = plan_lanes_; return; }
     size_t free_b = 0, total_b = 0;
     SSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -78,7 +78,9 @@ void Homotopy<T>::plan_batch(size_t batch, int kmax, bool host_path, size_t& chu
     // host-pointer entry: two lanes, so that one lane's copies, thin tail iterations and host round trips hide under
     // the other's kernels (C2: 84.4 -> 52.9 ms/step).  Device-pointer entry: one lane with the largest chunk (two lanes
     // gain 2 % there and blur the per-kernel event timing the roofline is computed from).
-    nlanes = (host_path && batch >= 8192) ? 2 : 1;
+    // Below ~32 K signals a lane's kernels are short enough (35-100 us) for the gaps between them to show: two lanes side by side fill
+    // them (8,192 signals: 4.69 -> 4.34 ms per step, 16,384: 8.17 -> 7.82) -- unless the per-kernel events are on.
+    nlanes = (host_path && batch >= 8192) ? 2 : (!host_path && !timing && batch >= 4096 && batch <= 32768) ? 2 : 1;
     if (const char* e = getenv("SSB200_LANES")) nlanes = std::max(1, std::min(MAX_LANES, atoi(e)));   // tuning knob
     size_t cap = std::max<size_t>(1, budget / nlanes / bytes_per_signal(kmax));
     size_t cap_max = 65536;
