@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
         } else {
             for (int i = tid; i < a.N; i += THREADS) mx0 = max(mx0, fabs(csrc[i]));
         }
-        mx0 = warp_max(mx0);
+        mx0 = warp_max_nonneg(mx0);
         if (lane == 0) red_v[warp] = mx0;   // read after the next barrier, rewritten only after the one that follows it
     }
     if constexpr (GS) {
@@ -560,13 +560,13 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             if (t > T(0) && t < TMAX && cand_less(t, i, best, bidx)) { best = t; bidx = i; }
         }
     }
-    warp_argmin(best, bidx);
+    warp_argmin_fast(best, bidx);
     if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
     __syncthreads();
     if (warp == 0) {
         best = lane < NW ? red_v[lane] : TMAX;
         bidx = lane < NW ? red_i[lane] : 0xffffffffu;
-        warp_argmin(best, bidx);
+        warp_argmin_fast(best, bidx);
         if (lane == 0) {
             sh_join = bidx != 0xffffffffu;
             if (bidx == 0xffffffffu) bidx = 0;   // no candidate: (max, 0) -- the caller toggles column 0 (:122-123)
@@ -656,7 +656,7 @@ __global__ void __launch_bounds__(THREADS) homotopy_step_kernel(HomArgs<T> a, in
             update(cc, qq, i0);
         }
     }
-    mx = warp_max(mx);
+    mx = warp_max_nonneg(mx);
     if (lane == 0) red_v[warp] = mx;
     if (!present) {
 #pragma unroll

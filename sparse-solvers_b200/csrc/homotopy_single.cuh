@@ -96,8 +96,6 @@ __global__ void __launch_bounds__(THREADS, 1) homotopy_single_kernel(SingleArgs<
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ T red_v[NW];
     __shared__ uint32_t red_i[NW];
-    __shared__ T sh_gamma, sh_lam;
-    __shared__ uint32_t sh_idx;
     __shared__ T xp_t[SINGLE_CLUSTER_MAX], xp_max[SINGLE_CLUSTER_MAX], xp_lam[SINGLE_CLUSTER_MAX];   // cluster form: the partials of every CTA, pushed by their owners
     __shared__ uint32_t xp_i[SINGLE_CLUSTER_MAX + 1];
 

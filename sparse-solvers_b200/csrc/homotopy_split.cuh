@@ -33,6 +33,7 @@ __device__ __forceinline__ void warp_argmin_flagged(T& v, uint32_t& i) {
 // candidate is strictly positive (or the FLT_MAX sentinel), so its bits order like its value; ties go to the lowest index, and the
 // one lane that holds the winner hands out its flag.  float64 keeps the shuffle form.
 __device__ __forceinline__ void warp_argmin_flagged_fast(float& v, uint32_t& i) {
+    if (SSB_SHUFFLE_REDUCE) { warp_argmin_flagged(v, i); return; }
     const uint32_t kv = __float_as_uint(v);
     const uint32_t mv = __reduce_min_sync(0xffffffffu, kv);
     const uint32_t mi = __reduce_min_sync(0xffffffffu, kv == mv ? (i & 0x7fffffffu) : 0xffffffffu);
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
         } else {
             for (int i = tid; i < a.N; i += THREADS) mx0 = max(mx0, fabs(csrc[i]));
         }
-        mx0 = warp_max(mx0);
+        mx0 = warp_max_nonneg(mx0);
         if (lane == 0) red_m[warp] = mx0;
         __syncthreads();
         lam = red_m[0];
@@ -214,13 +215,13 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             if (t > T(0) && t < TMAX && cand_less(t, gk[u], best, bidx & 0x7fffffffu)) { best = t; bidx = gk[u] | 0x80000000u; }
         }
     }
-    warp_argmin_flagged(best, bidx);
+    warp_argmin_flagged_fast(best, bidx);
     if (lane == 0) { red_v[warp] = best; red_i[warp] = bidx; }
     __syncthreads();
     if (warp == 0) {
         best = lane < NW ? red_v[lane] : TMAX;
         bidx = lane < NW ? red_i[lane] : 0xffffffffu;
-        warp_argmin_flagged(best, bidx);
+        warp_argmin_flagged_fast(best, bidx);
         if (lane == 0) {
             // no candidate: (max, 0) -- the caller toggles column 0 (:122-123), whichever side it is on
             sh_join = bidx != 0xffffffffu && !(bidx >> 31);
@@ -294,7 +295,7 @@ __global__ void __launch_bounds__(THREADS, SSB_SCAN_MINB * 128 / THREADS) homoto
             update(cc, qq, i0);
         }
     }
-    mx = warp_max(mx);
+    mx = warp_max_nonneg(mx);
     if (lane == 0) red_v[warp] = mx;
     __syncthreads();
     if (tid == 0) {
