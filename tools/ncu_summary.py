@@ -48,6 +48,8 @@ if traffic_out:
             continue
         tot = sum(float(r[idx[k]].replace(",", "")) * UNIT[units[idx[k]]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
         grid = r[idx["launch__grid_size"]]
+        if bn == "homotopy_algebra_kernel" and tot < out["bytes_per_launch"].get(bn, 0):
+            continue      # the late-iteration launch (the one that gathers p = A_G d) is the figure; a Gram-iteration launch moves 1/8 of it
         out["bytes_per_launch"][bn] = tot
         out["source"][bn] = f"{os.path.basename(rep)}: {r[idx['Kernel Name']][:70]}, grid {grid}, {r[idx['gpu__time_duration.sum']]} {units[idx['gpu__time_duration.sum']]}"
     json.dump(whole, open(traffic_out, "w"), indent=1)
