@@ -63,6 +63,11 @@ def test_noalloc_entry_on_a_padded_matrix_and_a_side_stream():
     assert _noalloc(torch, l, dW[:, :257], stream=side.cuda_stream) == 0, l.ssb200_last_error().decode()
     side.synchronize()
     np.testing.assert_allclose(dW.cpu().numpy(), want, rtol=8 * np.finfo(np.float32).eps, atol=0)
+    # the Python mirror's wrapper of the same entry (torch's current stream)
+    dV = torch.from_numpy(wide).cuda()
+    ss.norm_l1_noalloc(dV[:, :257])
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(dV.cpu().numpy(), dW.cpu().numpy())
 
 
 def test_noalloc_entry_refuses_what_the_static_scratch_cannot_hold():
