@@ -208,7 +208,7 @@ def run_reference(args, cfg):
     line = {
         "impl": "reference", "metric": "homotopy signals/sec", "value": value, "unit": "signals/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "strong" if (args.gpus > 1 and args.scaling == "strong") else "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: homotopy A {cfg['m']}x{cfg['n']} {cfg['dtype']}, {cfg['batch']} k={cfg['k']} signals "
                                + ("sharded over the GPUs" if (args.gpus > 1 and args.scaling == "strong") else "per GPU")
@@ -743,7 +743,7 @@ def run_b200(args, cfg):
     line = {
         "metric": "homotopy signals/sec", "value": world * batch * args.steps / (ms * 1e-3), "unit": "signals/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32" if dt == np.float32 else "f64",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32" if dt == np.float32 else "f64",
         "data": "synthetic",
         "config": {"workload": f"{args.config}: homotopy A {M}x{N} {cfg['dtype']}, {total} k={cfg['k']} signals "
                                + ("sharded over the GPUs" if strong else "per GPU") + f", tol {cfg['tol']}, max_iter {cfg['max_iter']}",
